@@ -1,0 +1,121 @@
+/* rt_b200.h -- C-ABI of the B200-native per-pixel render path (librt_b200.so).
+ *
+ * Drop-in boundary for zloyaloha/ray-tracing-practice.  The reference has no FFI; its seam is the C++ call
+ *     gpu_render(SceneParams&, SceneData&)            include/camera.cuh:114, src/camera.cu:290
+ *       -> Camera::render(color* d_fb)                src/camera.cu:198
+ *       -> render_kernel<<<grid,16x16>>>(color* fb)   src/camera.cu:17
+ * with its inputs in the host arrays create_scene fills (src/main.cu:346-497).  Every entry point below takes
+ * exactly those arrays, in the reference's own struct layouts, as plain pointers + sizes:
+ *     SphereData   32 B  {float center[3] @0; float radius @12; int material_idx @16}          include/sphere.h:8
+ *     PlaneData    80 B  {int type @0; float D @4; int material_idx @8; float w[3] @12, u[3] @24, v[3] @36,
+ *                         base[3] @48, normal[3] @60}                                          include/plane.h:9
+ *     MaterialData 64 B  {int type @0; float fuzz @4, ir @8; float absorption[3] @12, albedo[3] @24,
+ *                         emit[3] @36; u64 tex_obj @48; u64 cpu_tex @56 (both ignored here)}   include/materials.h:53
+ *     CameraData   76 B  {float origin[3], pixel00_loc[3], pixel_delta_u[3], pixel_delta_v[3], background[3];
+ *                         int image_width, image_height, samples_per_pixel, max_depth}         include/camera.cuh:86
+ * The library owns all device memory behind an opaque handle; the caller owns every host buffer.
+ * All functions return RT_OK (0) or an RT_ERR_* code; rt_last_error() gives the message (thread-local).
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails with RT_ERR_NO_DEVICE.
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rt_scene rt_scene;
+
+enum {
+    RT_OK = 0,
+    RT_ERR_INVALID = 1,     /* bad argument (null pointer, negative count, material index out of range ...) */
+    RT_ERR_CUDA = 2,        /* a CUDA runtime call failed; message carries file:line and the CUDA error string */
+    RT_ERR_NO_DEVICE = 3,   /* no usable CUDA device (the reference would exit(99), include/camera.cuh:20-29) */
+    RT_ERR_UNSUPPORTED = 4
+};
+
+enum { RT_KERNEL_MEGA = 0, RT_KERNEL_WAVEFRONT = 1 };
+enum { RT_RNG_PHILOX = 0,      /* counter-based Philox4x32-10 keyed on (seed; pixel, sample, bounce) -- production */
+       RT_RNG_REFERENCE = 1 }; /* the reference's stateful wang_hash stream (include/random_utils.h) incl. its
+                                  rejection loops -- parity mode: reproduces the reference host render per sample */
+enum { RT_TEX_CPU = 0,         /* tex2D_cpu semantics: V flipped, no half texel (include/materials.h:20-51) */
+       RT_TEX_GPU = 1 };       /* CUDA texture unit as the reference sets it up (src/main.cu:37-43) -- default */
+
+typedef struct rt_render_opts {
+    int struct_size;            /* = sizeof(rt_render_opts); 0-filled tail fields take defaults */
+    int kernel;                 /* RT_KERNEL_* */
+    int rng;                    /* RT_RNG_* */
+    int exact_math;             /* 1: leaf tests + shading in the reference host build's exact operation order
+                                   (no FMA contraction, double where the reference widens); 0: fast fp32 */
+    int tex_mode;               /* RT_TEX_* */
+    unsigned long long seed;    /* Philox key (ignored by RT_RNG_REFERENCE, which is keyed by pixel like the reference) */
+    int tile_rank, tile_nranks; /* interleaved-tile partition: this call renders tiles t with t % nranks == rank.
+                                   nranks <= 1 renders everything.  Pixels of other ranks are left untouched. */
+    int count_work;             /* 1: also count node visits / leaf tests / shaded hits (slower; for the roofline) */
+    int top_nodes_in_smem;      /* -1 default; 0 off; N>0: stage the first N wide nodes in shared memory */
+} rt_render_opts;
+
+typedef struct rt_work_counters {
+    unsigned long long segments;      /* path segments = hit_scene calls (the "rays" of the Mrays/s metric) */
+    unsigned long long node_visits;   /* wide nodes fetched */
+    unsigned long long sphere_tests;
+    unsigned long long plane_tests;
+    unsigned long long shaded_hits;
+    unsigned long long samples;
+} rt_work_counters;
+
+typedef struct rt_scene_stats {
+    int num_spheres, num_planes, num_materials;
+    int wide_nodes, wide_depth, max_stack, leaves;
+    float sah_cost, build_ms, upload_ms;
+    unsigned long long device_bytes;
+} rt_scene_stats;
+
+/* Replaces create_scene's upload + build_bvh (src/main.cu:428-478, include/bvh_builder.h:99): copies the three
+ * arrays, builds the wide BVH and SoA primitive buffers, uploads.  tex_rgba: tw*th RGBA float texels exactly as
+ * stbi_loadf(...,4) returns them (src/main.cu:18), applied to materials[tex_material_idx]; NULL/-1 for none. */
+int rt_scene_create(const void* spheres, int num_spheres, const void* planes, int num_planes, const void* materials,
+                    int num_materials, const float* tex_rgba, int tex_w, int tex_h, int tex_material_idx, rt_scene** out);
+/* Replaces destroy_scene_arrays + destroy_all_materials (src/main.cu:310-344). */
+void rt_scene_destroy(rt_scene* scene);
+int rt_scene_get_stats(const rt_scene* scene, rt_scene_stats* out);
+
+/* Replaces Camera::render up to and including its D2H copy (src/camera.cu:198-209): renders one frame and
+ * writes fb_sum_rgb[(j*W+i)*3+c] = SUM over samples of radiance (the reference's framebuffer contract,
+ * src/camera.cu:33) into HOST memory.  opts may be NULL (defaults: megakernel, Philox seed 0, fast math, GPU
+ * texture semantics).  ray_segments / kernel_ms / counters may be NULL. */
+int rt_render(rt_scene* scene, const void* camera_data76, const rt_render_opts* opts, float* fb_sum_rgb,
+              unsigned long long* ray_segments, float* kernel_ms, rt_work_counters* counters);
+/* Same, framebuffer stays in DEVICE memory (d_fb_sum_rgb: W*H*3 floats) and the launch is asynchronous on
+ * `cuda_stream` (a cudaStream_t, may be NULL).  Counters are fetched by rt_render_finish. */
+int rt_render_device(rt_scene* scene, const void* camera_data76, const rt_render_opts* opts, void* d_fb_sum_rgb,
+                     void* cuda_stream);
+int rt_render_finish(rt_scene* scene, unsigned long long* ray_segments, float* kernel_ms, rt_work_counters* counters);
+
+/* Closest hit with primitive ids for caller-supplied rays (host arrays; rays6 = N x {ox,oy,oz,dx,dy,dz}).
+ * prim_type: 0 sphere / 1 plane / -1 miss (BVHNode::type convention, include/bvh.h:11); prim_index: index into
+ * the caller's original array; t: hit parameter in units of the UNNORMALISED direction, like HitRecord::t.
+ * Always runs the exact-math leaf tests; parity target: the reference's leaf tests over all primitives. */
+int rt_trace_primary(rt_scene* scene, const float* rays6, int num_rays, float tmin, float tmax, int* prim_type,
+                     int* prim_index, float* t);
+
+/* Device-side output stage replacing ISaver::writeColor's arithmetic (src/camera.cu:136-148): byte =
+ * (unsigned char)(256*clamp(sqrt(sum/divisor),0,0.999)).  d_fb_sum_rgb is a device pointer, rgb_u8 a host one. */
+int rt_tonemap_u8(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int divisor, unsigned char* rgb_u8);
+
+/* Tile partition helpers for the multi-GPU frame (tiles are RT_TILE x RT_TILE pixels, row-major tile ids). */
+#define RT_TILE 16
+int rt_tiles_pack(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int rank, int nranks, void* d_packed,
+                  void* cuda_stream);
+int rt_tiles_unpack(rt_scene* scene, const void* d_packed_all, int width, int height, int nranks, void* d_fb_sum_rgb,
+                    void* cuda_stream);
+unsigned long long rt_tiles_packed_floats(int width, int height, int nranks); /* per-rank packed buffer length */
+
+const char* rt_last_error(void);
+int rt_device_count(void);
+const char* rt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,245 @@
+// kernels.cu -- the sm_100a kernels of the per-pixel render path.
+//
+// render_mega replaces the reference's render_kernel + ray_color (src/camera.cu:17-34, 218-252).  The reference
+// maps one thread to one pixel and runs its whole spp x depth loop nest there, so a warp lives as long as its
+// slowest pixel and dead lanes idle through every bounce.  Here the kernel is PERSISTENT (one grid sized to the
+// machine: SMs x resident CTAs) and every loop iteration advances every lane by exactly one path segment:
+//   * a lane whose path ended regenerates the next sample of ITS pixel in the same iteration, so lanes never idle
+//     on path-length variance (62 % of paths end at the first vertex, the tail runs to max_depth);
+//   * a lane whose pixel is complete takes the next pixel of its warp's 16x16 tile; a warp whose tile is used up
+//     fetches the next tile id with ONE atomicAdd (lane 0) and a shuffle broadcast -- work fetch is
+//     warp-aggregated, ballot/popc ranks hand the pixels of the tile to the lanes that need one;
+//   * per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored
+//     once, so the output is deterministic and, in parity mode, comparable bit for bit.
+#include "kernels.h"
+#include "path.cuh"
+
+namespace rtb {
+
+// stage the top of the BVH: wide nodes [0, top) -> shared memory, 9 x float4 stride
+__device__ __forceinline__ void stage_top_nodes(const DevScene& sc, float4* s_top) {
+    int n4 = sc.top_nodes * 8;
+    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+        int node = i >> 3, k = i & 7;
+        s_top[node * kTopStride + k] = __ldg(sc.nodes + i);
+    }
+    __syncthreads();
+}
+
+template <int MODE, bool X, bool COUNT>
+__global__ void __launch_bounds__(256, 2) render_mega(const __grid_constant__ DevScene sc, const __grid_constant__ FrameParams fp) {
+    extern __shared__ float4 smem4[];
+    float4* s_top = smem4;
+    float* s_st = reinterpret_cast<float*>(smem4 + sc.top_nodes * kTopStride);
+    int* s_sr = reinterpret_cast<int*>(s_st + kSmemStack * blockDim.x);
+    stage_top_nodes(sc, s_top);
+
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int W = fp.cam.W, H = fp.cam.H, spp = fp.cam.spp;
+
+    // warp-uniform tile pool
+    int pool_tile = 0, pool_next = kTile * kTile;
+    bool exhausted = false;
+
+    // per-lane path state
+    bool has_pixel = false;
+    int px = 0, py = 0, sample = 0;
+    PathState ps;
+    ps.o = mk3(0, 0, 0); ps.d = mk3(0, 0, 1); ps.beta = mk3(1, 1, 1); ps.L = mk3(0, 0, 0); ps.depth = 0;
+    V3 acc = mk3(0, 0, 0);
+    Rng<MODE> rng;
+    uint32_t pixel_base = 0;
+    bool new_sample = false;
+    WorkCount wc = {0, 0, 0, 0, 0, 0};
+
+    for (;;) {
+        // ---- 1. hand out pixels to lanes that have none (warp-aggregated fetch)
+        unsigned need = __ballot_sync(full, !has_pixel);
+        while (need && !exhausted) {
+            if (pool_next >= kTile * kTile) {
+                unsigned k = 0;
+                if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
+                k = __shfl_sync(full, k, 0);
+                if ((int)k >= fp.my_tiles) { exhausted = true; break; }
+                pool_tile = (int)k * fp.tile_nranks + fp.tile_rank;
+                pool_next = 0;
+            }
+            int avail = kTile * kTile - pool_next;
+            int rank = __popc(need & ((1u << lane) - 1u));
+            if (!has_pixel && rank < avail) {
+                int q = pool_next + rank;
+                int blk = q >> 5;  // 8 blocks of 8x4 pixels inside the 16x16 tile
+                int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
+                int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
+                if (x < W && y < H) {
+                    has_pixel = true;
+                    px = x; py = y;
+                    sample = 0;
+                    acc = mk3(0, 0, 0);
+                    new_sample = true;
+                    pixel_base = pixel_seed_base(x, y, W);
+                }
+            }
+            int n_need = __popc(need);
+            pool_next += n_need < avail ? n_need : avail;
+            need = __ballot_sync(full, !has_pixel);
+        }
+        if (!__any_sync(full, has_pixel)) break;
+
+        if (has_pixel) {
+            // ---- 2. start a sample
+            if (new_sample) {
+                begin_path<MODE, X>(fp.cam, px, py, sample, pixel_base, fp.key, rng, ps);
+                new_sample = false;
+                if (COUNT) wc.samples++;
+            }
+            // ---- 3. one path segment
+            if (advance_path<MODE, X, COUNT>(sc, fp.cam, fp.tex_mode, s_top, s_st, s_sr, ps, rng, wc)) {
+                // ---- 4. sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
+                acc = add3<X>(acc, ps.L);
+                ++sample;
+                new_sample = true;
+                if (sample >= spp) {
+                    float* out = fp.fb + 3 * ((size_t)py * W + px);
+                    out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
+                    has_pixel = false;
+                }
+            }
+        }
+    }
+
+    // ---- work counters: warp reduce, one atomic per warp and counter
+    unsigned int vals[6] = {wc.segments, wc.nodes, wc.spheres, wc.planes, wc.hits, wc.samples};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        if (!COUNT && i != 0) continue;
+        unsigned long long v = vals[i];
+        for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
+        if (lane == 0 && v) atomicAdd(fp.counters + i, v);
+    }
+}
+
+size_t mega_smem_bytes(int top_nodes, int threads) {
+    return (size_t)top_nodes * kTopStride * sizeof(float4) + (size_t)kSmemStack * threads * (sizeof(float) + sizeof(int));
+}
+
+template <int MODE, bool X, bool COUNT>
+static cudaError_t launch_mega_t(const DevScene& sc, const FrameParams& fp, LaunchCfg cfg, cudaStream_t stream) {
+    size_t smem = mega_smem_bytes(sc.top_nodes, cfg.threads);
+    cudaError_t e = cudaFuncSetAttribute(render_mega<MODE, X, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    render_mega<MODE, X, COUNT><<<cfg.num_sms * cfg.blocks_per_sm, cfg.threads, smem, stream>>>(sc, fp);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
+                               cudaStream_t stream) {
+    int sel = (rng ? 4 : 0) | (exact ? 2 : 0) | (count ? 1 : 0);
+    switch (sel) {
+        case 0: return launch_mega_t<kRngPhilox, false, false>(sc, fp, cfg, stream);
+        case 1: return launch_mega_t<kRngPhilox, false, true>(sc, fp, cfg, stream);
+        case 2: return launch_mega_t<kRngPhilox, true, false>(sc, fp, cfg, stream);
+        case 3: return launch_mega_t<kRngPhilox, true, true>(sc, fp, cfg, stream);
+        case 4: return launch_mega_t<kRngReference, false, false>(sc, fp, cfg, stream);
+        case 5: return launch_mega_t<kRngReference, false, true>(sc, fp, cfg, stream);
+        case 6: return launch_mega_t<kRngReference, true, false>(sc, fp, cfg, stream);
+        default: return launch_mega_t<kRngReference, true, true>(sc, fp, cfg, stream);
+    }
+}
+
+// ---------------------------------------------------------------- primary-ray closest hit (parity entry point)
+__global__ void __launch_bounds__(256, 2) trace_primary_kernel(const __grid_constant__ DevScene sc, const float* __restrict__ rays6,
+                                                               int n, float tmin, float tmax, int* __restrict__ type,
+                                                               int* __restrict__ index, float* __restrict__ t) {
+    extern __shared__ float4 smem4[];
+    float4* s_top = smem4;
+    float* s_st = reinterpret_cast<float*>(smem4 + sc.top_nodes * kTopStride);
+    int* s_sr = reinterpret_cast<int*>(s_st + kSmemStack * blockDim.x);
+    stage_top_nodes(sc, s_top);
+    WorkCount wc = {0, 0, 0, 0, 0, 0};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float* r = rays6 + 6 * (size_t)i;
+        HitInfo hit;
+        trace_closest<true, false>(sc, s_top, s_st, s_sr, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), tmin, tmax, hit, wc);
+        type[i] = hit.type;
+        index[i] = hit.orig;
+        t[i] = hit.type < 0 ? 0.0f : hit.t;
+    }
+}
+
+cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
+                                 int* d_index, float* d_t, cudaStream_t stream) {
+    const int threads = 256;
+    size_t smem = mega_smem_bytes(sc.top_nodes, threads);
+    cudaError_t e = cudaFuncSetAttribute(trace_primary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int blocks = (n + threads - 1) / threads;
+    if (blocks > 148 * 2 * 4) blocks = 148 * 2 * 4;
+    if (blocks < 1) blocks = 1;
+    trace_primary_kernel<<<blocks, threads, smem, stream>>>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- output stage (ISaver::writeColor arithmetic)
+// src/camera.cu:136-148: c/=N (multiply by the double reciprocal narrowed), sqrt, clamp [0,0.999], *256, truncate
+__global__ void tonemap_kernel(const float* __restrict__ fb, size_t n, float inv_div, unsigned char* __restrict__ out) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        float v = __fsqrt_rn(__fmul_rn(inv_div, fb[i]));
+        v = v < 0.0f ? 0.0f : (v > 0.999f ? 0.999f : v);
+        out[i] = (unsigned char)(int)__fmul_rn(256.0f, v);
+    }
+}
+cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, cudaStream_t stream) {
+    float inv = (float)(1.0 / (double)(float)divisor);
+    int blocks = (int)((n_values + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    tonemap_kernel<<<blocks, 256, 0, stream>>>(d_fb, n_values, inv, d_out);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- tile pack / unpack for the multi-GPU gather
+// rank r owns tiles t with t % nranks == r; its packed buffer holds them in increasing t, 16x16x3 floats each.
+size_t tiles_packed_floats(int W, int H, int nranks) {
+    size_t tiles = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
+    size_t per = (tiles + nranks - 1) / nranks;
+    return per * kTile * kTile * 3;
+}
+__global__ void tiles_pack_kernel(const float* __restrict__ fb, int W, int H, int rank, int nranks, float* __restrict__ packed) {
+    int tiles_x = (W + kTile - 1) / kTile, tiles_y = (H + kTile - 1) / kTile;
+    int my = (tiles_x * tiles_y - rank + nranks - 1) / nranks;
+    for (int k = blockIdx.x; k < my; k += gridDim.x) {
+        int t = k * nranks + rank;
+        int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
+        float* dst = packed + ((size_t)k * kTile * kTile + threadIdx.x) * 3;
+        if (x < W && y < H) {
+            const float* src = fb + 3 * ((size_t)y * W + x);
+            dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+        } else {
+            dst[0] = dst[1] = dst[2] = 0.0f;
+        }
+    }
+}
+__global__ void tiles_unpack_kernel(const float* __restrict__ all, int W, int H, int nranks, size_t per_rank, float* __restrict__ fb) {
+    int tiles_x = (W + kTile - 1) / kTile, tiles_y = (H + kTile - 1) / kTile;
+    for (int t = blockIdx.x; t < tiles_x * tiles_y; t += gridDim.x) {
+        int r = t % nranks, k = t / nranks;
+        int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
+        if (x < W && y < H) {
+            const float* src = all + (size_t)r * per_rank + ((size_t)k * kTile * kTile + threadIdx.x) * 3;
+            float* dst = fb + 3 * ((size_t)y * W + x);
+            dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+        }
+    }
+}
+cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, cudaStream_t stream) {
+    tiles_pack_kernel<<<148 * 4, kTile * kTile, 0, stream>>>(d_fb, W, H, rank, nranks, d_packed);
+    return cudaGetLastError();
+}
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, float* d_fb, cudaStream_t stream) {
+    tiles_unpack_kernel<<<148 * 4, kTile * kTile, 0, stream>>>(d_packed_all, W, H, nranks, tiles_packed_floats(W, H, nranks), d_fb);
+    return cudaGetLastError();
+}
+
+}  // namespace rtb

@@ -1,0 +1,47 @@
+// kernels.h -- host-visible launch interface of the sm_100a kernels (kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "path.cuh"
+
+namespace rtb {
+
+struct FrameParams {
+    CameraPod cam;
+    uint2 key;          // Philox key
+    int tex_mode;       // 0 cpu semantics, 1 texture unit
+    int tile_rank, tile_nranks;
+    int tiles_x, tiles_y, my_tiles;
+    float* fb;                        // W*H*3 sums
+    unsigned int* tile_counter;       // work queue head (zeroed before launch)
+    unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
+};
+
+struct LaunchCfg {
+    int num_sms;
+    int blocks_per_sm;
+    int threads;
+};
+
+constexpr int kTile = 16;  // == RT_TILE
+
+// persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1
+cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
+                               cudaStream_t stream);
+// wavefront variant (generate / extend / shade kernels over global queues); scratch is owned by the caller
+struct WavefrontScratch {
+    void* buf = nullptr;
+    size_t bytes = 0;
+};
+cudaError_t launch_render_wavefront(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
+                                    WavefrontScratch& scratch, cudaStream_t stream);
+cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
+                                 int* d_index, float* d_t, cudaStream_t stream);
+cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, cudaStream_t stream);
+cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, cudaStream_t stream);
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, float* d_fb, cudaStream_t stream);
+size_t tiles_packed_floats(int W, int H, int nranks);
+size_t mega_smem_bytes(int top_nodes, int threads);
+
+}  // namespace rtb

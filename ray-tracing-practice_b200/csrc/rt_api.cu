@@ -1,0 +1,390 @@
+// rt_api.cu -- the C-ABI declared in include/rt_b200.h: scene upload, frame launch, parity trace, output stage.
+// Owns every device allocation behind the opaque rt_scene handle (the reference leaves them to the caller and
+// leaks the BVH node array, src/main.cu:453-474 vs :322-344).  No CPU fallback: every compute entry point needs
+// a CUDA device and fails with RT_ERR_NO_DEVICE / RT_ERR_CUDA otherwise.
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rt_b200.h"
+#include "kernels.h"
+#include "scene_pack.h"
+#include "wide_bvh.h"
+
+using namespace rtb;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define RT_CUDA(expr)                                                                                              \
+    do {                                                                                                           \
+        cudaError_t e_ = (expr);                                                                                   \
+        if (e_ != cudaSuccess) {                                                                                   \
+            char b_[512];                                                                                          \
+            snprintf(b_, sizeof b_, "CUDA error = %u (%s) at %s:%d '%s'", (unsigned)e_, cudaGetErrorString(e_), __FILE__, \
+                     __LINE__, #expr);                                                                             \
+            cudaGetLastError();                                                                                    \
+            return fail(RT_ERR_CUDA, b_);                                                                          \
+        }                                                                                                          \
+    } while (0)
+
+}  // namespace
+
+struct rt_scene {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    rt_scene_stats stats{};
+    DevScene dev{};
+    int default_top = 0;
+    // owned device memory
+    void* d_nodes = nullptr;
+    void* d_spheres = nullptr;
+    void* d_sphere_meta = nullptr;
+    void* d_planes = nullptr;
+    void* d_mats = nullptr;
+    void* d_tex = nullptr;
+    cudaArray_t tex_array = nullptr;
+    cudaTextureObject_t tex_obj = 0;
+    float* d_fb = nullptr;
+    size_t fb_floats = 0;
+    unsigned char* d_u8 = nullptr;
+    size_t u8_bytes = 0;
+    unsigned int* d_tile_counter = nullptr;
+    unsigned long long* d_counters = nullptr;
+    void* d_trace = nullptr;
+    size_t trace_bytes = 0;
+    WavefrontScratch wf;
+    bool pending = false;
+    cudaStream_t pending_stream = nullptr;
+};
+
+static int check_device() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        return fail(RT_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    }
+    return RT_OK;
+}
+
+extern "C" {
+
+const char* rt_last_error(void) { return g_err.c_str(); }
+const char* rt_version(void) { return "rt_b200 0.1 (sm_100a)"; }
+int rt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+static int upload(void** dst, const void* src, size_t bytes, unsigned long long& total) {
+    *dst = nullptr;
+    size_t alloc = bytes ? bytes : 16;
+    RT_CUDA(cudaMalloc(dst, alloc));
+    if (bytes) RT_CUDA(cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice));
+    total += alloc;
+    return RT_OK;
+}
+
+int rt_scene_create(const void* spheres, int S, const void* planes, int P, const void* materials, int M, const float* tex_rgba,
+                    int tw, int th, int tex_mat, rt_scene** out) {
+    if (!out) return fail(RT_ERR_INVALID, "rt_scene_create: out is NULL");
+    *out = nullptr;
+    if (S < 0 || P < 0 || M <= 0) return fail(RT_ERR_INVALID, "rt_scene_create: negative primitive count or no materials");
+    if ((S && !spheres) || (P && !planes) || !materials) return fail(RT_ERR_INVALID, "rt_scene_create: NULL array");
+    if ((long long)S >= (1 << 28) || (long long)P >= (1 << 28)) return fail(RT_ERR_INVALID, "rt_scene_create: too many primitives");
+    const SphereIn* sp = (const SphereIn*)spheres;
+    const PlaneIn* pl = (const PlaneIn*)planes;
+    const MatIn* mt = (const MatIn*)materials;
+    for (int i = 0; i < S; ++i)
+        if (sp[i].mat < 0 || sp[i].mat >= M) return fail(RT_ERR_INVALID, "rt_scene_create: sphere material_idx out of range");
+    for (int i = 0; i < P; ++i) {
+        if (pl[i].mat < 0 || pl[i].mat >= M) return fail(RT_ERR_INVALID, "rt_scene_create: plane material_idx out of range");
+        if (pl[i].type < 0 || pl[i].type > 2) return fail(RT_ERR_INVALID, "rt_scene_create: plane type must be QUAD/ELLIPSE/TRIANGLE");
+    }
+    for (int i = 0; i < M; ++i)
+        if (mt[i].type < 0 || mt[i].type > 3) return fail(RT_ERR_INVALID, "rt_scene_create: unknown material type");
+    if (tex_rgba && (tw <= 0 || th <= 0 || tex_mat < 0 || tex_mat >= M))
+        return fail(RT_ERR_INVALID, "rt_scene_create: bad texture size or material index");
+    int rc = check_device();
+    if (rc) return rc;
+
+    // ---- wide BVH over conservative boxes + SoA primitive buffers in leaf order (host, scene_pack.cpp)
+    auto t1 = std::chrono::steady_clock::now();
+    PackedScene pk = pack_scene(sp, S, pl, P, mt, M);
+    const WideBvh& bvh = pk.bvh;
+    if (bvh.max_stack > kSmemStack + kLocalStack)
+        return fail(RT_ERR_UNSUPPORTED, "rt_scene_create: BVH needs a deeper traversal stack than the kernels provide");
+
+    rt_scene* s = new rt_scene();
+    auto bail = [&](int code) { rt_scene_destroy(s); return code; };
+    cudaGetDevice(&s->device);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) s->num_sms = prop.multiProcessorCount;
+    unsigned long long total = 0;
+    if ((rc = upload(&s->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(WideNode), total))) return bail(rc);
+    if ((rc = upload(&s->d_spheres, pk.spheres.data(), pk.spheres.size() * sizeof(float), total))) return bail(rc);
+    if ((rc = upload(&s->d_sphere_meta, pk.sphere_meta.data(), pk.sphere_meta.size() * sizeof(int), total))) return bail(rc);
+    if ((rc = upload(&s->d_planes, pk.planes.data(), pk.planes.size() * sizeof(float), total))) return bail(rc);
+    if ((rc = upload(&s->d_mats, pk.mats.data(), pk.mats.size() * sizeof(float), total))) return bail(rc);
+    s->dev.tex_mat = -1;
+    if (tex_rgba) {
+        size_t bytes = (size_t)tw * th * 4 * sizeof(float);
+        if ((rc = upload(&s->d_tex, tex_rgba, bytes, total))) return bail(rc);
+        // texture object with the reference's descriptor (src/main.cu:24-46): float4 array, wrap, linear, normalised
+        cudaChannelFormatDesc cd = cudaCreateChannelDesc(32, 32, 32, 32, cudaChannelFormatKindFloat);
+        auto chk = [&](cudaError_t e, const char* what) {
+            if (e == cudaSuccess) return 0;
+            cudaGetLastError();
+            return fail(RT_ERR_CUDA, std::string("CUDA error (") + cudaGetErrorString(e) + ") in " + what);
+        };
+        if ((rc = chk(cudaMallocArray(&s->tex_array, &cd, tw, th), "cudaMallocArray"))) return bail(rc);
+        size_t pitch = (size_t)tw * 4 * sizeof(float);
+        if ((rc = chk(cudaMemcpy2DToArray(s->tex_array, 0, 0, tex_rgba, pitch, pitch, th, cudaMemcpyHostToDevice), "cudaMemcpy2DToArray")))
+            return bail(rc);
+        cudaResourceDesc rd;
+        memset(&rd, 0, sizeof rd);
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = s->tex_array;
+        cudaTextureDesc td;
+        memset(&td, 0, sizeof td);
+        td.addressMode[0] = cudaAddressModeWrap;
+        td.addressMode[1] = cudaAddressModeWrap;
+        td.filterMode = cudaFilterModeLinear;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 1;
+        if ((rc = chk(cudaCreateTextureObject(&s->tex_obj, &rd, &td, nullptr), "cudaCreateTextureObject"))) return bail(rc);
+        total += bytes;
+        s->dev.tex_mat = tex_mat;
+        s->dev.tex_w = tw;
+        s->dev.tex_h = th;
+    }
+    auto chk2 = [&](cudaError_t e) { if (e != cudaSuccess) { cudaGetLastError(); fail(RT_ERR_CUDA, cudaGetErrorString(e)); return 1; } return 0; };
+    if (chk2(cudaMalloc((void**)&s->d_tile_counter, 64)) || chk2(cudaMalloc((void**)&s->d_counters, 64)) ||
+        chk2(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) || chk2(cudaEventCreate(&s->ev0)) ||
+        chk2(cudaEventCreate(&s->ev1)))
+        return bail(RT_ERR_CUDA);
+    auto t2 = std::chrono::steady_clock::now();
+
+    s->dev.nodes = (const float4*)s->d_nodes;
+    s->dev.spheres = (const float4*)s->d_spheres;
+    s->dev.sphere_meta = (const int2*)s->d_sphere_meta;
+    s->dev.planes = (const float4*)s->d_planes;
+    s->dev.mats = (const float4*)s->d_mats;
+    s->dev.tex = (const float4*)s->d_tex;
+    s->dev.tex_obj = s->tex_obj;
+    s->dev.num_nodes = (int)bvh.nodes.size();
+    s->default_top = s->dev.num_nodes < 64 ? s->dev.num_nodes : 64;
+    s->dev.top_nodes = s->default_top;
+
+    s->stats.num_spheres = S;
+    s->stats.num_planes = P;
+    s->stats.num_materials = M;
+    s->stats.wide_nodes = (int)bvh.nodes.size();
+    s->stats.wide_depth = bvh.depth;
+    s->stats.max_stack = bvh.max_stack;
+    s->stats.leaves = bvh.leaves;
+    s->stats.sah_cost = bvh.sah_cost;
+    s->stats.build_ms = pk.build_ms;
+    s->stats.upload_ms = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    s->stats.device_bytes = total;
+    *out = s;
+    return RT_OK;
+}
+
+void rt_scene_destroy(rt_scene* s) {
+    if (!s) return;
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
+    if (s->tex_array) cudaFreeArray(s->tex_array);
+    void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
+                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf};
+    for (void* b : bufs)
+        if (b) cudaFree(b);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    cudaGetLastError();
+    delete s;
+}
+
+int rt_scene_get_stats(const rt_scene* s, rt_scene_stats* out) {
+    if (!s || !out) return fail(RT_ERR_INVALID, "rt_scene_get_stats: NULL argument");
+    *out = s->stats;
+    return RT_OK;
+}
+
+static rt_render_opts resolve_opts(const rt_render_opts* in) {
+    rt_render_opts o;
+    memset(&o, 0, sizeof o);
+    o.tex_mode = RT_TEX_GPU;
+    o.top_nodes_in_smem = -1;
+    o.tile_nranks = 1;
+    if (in) {
+        size_t n = in->struct_size > 0 && (size_t)in->struct_size < sizeof o ? (size_t)in->struct_size : sizeof o;
+        memcpy(&o, in, n);
+        if (n < sizeof o) {  // fields beyond the caller's struct keep their defaults
+            rt_render_opts d;
+            memset(&d, 0, sizeof d);
+            d.tex_mode = RT_TEX_GPU;
+            d.top_nodes_in_smem = -1;
+            d.tile_nranks = 1;
+            memcpy((char*)&o + n, (char*)&d + n, sizeof o - n);
+        }
+    }
+    if (o.tile_nranks < 1) o.tile_nranks = 1;
+    return o;
+}
+
+static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, float* d_fb, cudaStream_t stream) {
+    if (!s || !cam76 || !d_fb) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
+    rt_render_opts o = resolve_opts(opts_in);
+    FrameParams fp;
+    memset(&fp, 0, sizeof fp);
+    memcpy(&fp.cam, cam76, sizeof(CameraPod));
+    if (fp.cam.W <= 0 || fp.cam.H <= 0 || fp.cam.spp < 0 || fp.cam.depth < 0) return fail(RT_ERR_INVALID, "rt_render: bad CameraData");
+    if (o.tile_rank < 0 || o.tile_rank >= o.tile_nranks) return fail(RT_ERR_INVALID, "rt_render: tile_rank out of range");
+    if (o.kernel != RT_KERNEL_MEGA && o.kernel != RT_KERNEL_WAVEFRONT) return fail(RT_ERR_INVALID, "rt_render: unknown kernel");
+    fp.key = make_uint2((unsigned)(o.seed & 0xffffffffu), (unsigned)(o.seed >> 32));
+    fp.tex_mode = o.tex_mode;
+    fp.tile_rank = o.tile_rank;
+    fp.tile_nranks = o.tile_nranks;
+    fp.tiles_x = (fp.cam.W + kTile - 1) / kTile;
+    fp.tiles_y = (fp.cam.H + kTile - 1) / kTile;
+    int tiles = fp.tiles_x * fp.tiles_y;
+    fp.my_tiles = tiles > o.tile_rank ? (tiles - o.tile_rank + o.tile_nranks - 1) / o.tile_nranks : 0;
+    fp.fb = d_fb;
+    fp.tile_counter = s->d_tile_counter;
+    fp.counters = s->d_counters;
+    DevScene dev = s->dev;
+    int top = o.top_nodes_in_smem < 0 ? s->default_top : o.top_nodes_in_smem;
+    if (top > dev.num_nodes) top = dev.num_nodes;
+    if (top > 1024) top = 1024;
+    dev.top_nodes = top;
+    LaunchCfg cfg{s->num_sms, 2, 256};
+    RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, 64, stream));
+    RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
+    RT_CUDA(cudaEventRecord(s->ev0, stream));
+    if (o.kernel == RT_KERNEL_MEGA) RT_CUDA(launch_render_mega(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
+    else RT_CUDA(launch_render_wavefront(dev, fp, o.rng, o.exact_math, o.count_work, cfg, s->wf, stream));
+    RT_CUDA(cudaEventRecord(s->ev1, stream));
+    s->pending = true;
+    s->pending_stream = stream;
+    return RT_OK;
+}
+
+int rt_render_finish(rt_scene* s, unsigned long long* segs, float* kernel_ms, rt_work_counters* counters) {
+    if (!s) return fail(RT_ERR_INVALID, "rt_render_finish: NULL scene");
+    if (!s->pending) return fail(RT_ERR_INVALID, "rt_render_finish: no frame in flight");
+    RT_CUDA(cudaEventSynchronize(s->ev1));
+    s->pending = false;
+    unsigned long long c[8];
+    RT_CUDA(cudaMemcpyAsync(c, s->d_counters, 48, cudaMemcpyDeviceToHost, s->pending_stream));
+    RT_CUDA(cudaStreamSynchronize(s->pending_stream));
+    if (segs) *segs = c[0];
+    if (kernel_ms) RT_CUDA(cudaEventElapsedTime(kernel_ms, s->ev0, s->ev1));
+    if (counters) {
+        counters->segments = c[0]; counters->node_visits = c[1]; counters->sphere_tests = c[2];
+        counters->plane_tests = c[3]; counters->shaded_hits = c[4]; counters->samples = c[5];
+    }
+    return RT_OK;
+}
+
+int rt_render_device(rt_scene* s, const void* cam76, const rt_render_opts* opts, void* d_fb, void* cuda_stream) {
+    return launch_frame(s, cam76, opts, (float*)d_fb, (cudaStream_t)cuda_stream);
+}
+
+int rt_render(rt_scene* s, const void* cam76, const rt_render_opts* opts, float* fb, unsigned long long* segs, float* kernel_ms,
+              rt_work_counters* counters) {
+    if (!s || !cam76 || !fb) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
+    CameraPod cam;
+    memcpy(&cam, cam76, sizeof cam);
+    if (cam.W <= 0 || cam.H <= 0) return fail(RT_ERR_INVALID, "rt_render: bad CameraData");
+    size_t n = (size_t)cam.W * cam.H * 3;
+    if (s->fb_floats < n) {
+        if (s->d_fb) cudaFree(s->d_fb);
+        s->d_fb = nullptr;
+        s->fb_floats = 0;
+        RT_CUDA(cudaMalloc((void**)&s->d_fb, n * sizeof(float)));
+        s->fb_floats = n;
+    }
+    rt_render_opts o = resolve_opts(opts);
+    if (o.tile_nranks > 1) RT_CUDA(cudaMemsetAsync(s->d_fb, 0, n * sizeof(float), s->stream));
+    int rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
+    if (rc) return rc;
+    RT_CUDA(cudaMemcpyAsync(fb, s->d_fb, n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
+    rc = rt_render_finish(s, segs, kernel_ms, counters);
+    if (rc) return rc;
+    RT_CUDA(cudaStreamSynchronize(s->stream));
+    return RT_OK;
+}
+
+int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float tmax, int* type, int* index, float* t) {
+    if (!s || (n > 0 && (!rays6 || !type || !index || !t)) || n < 0) return fail(RT_ERR_INVALID, "rt_trace_primary: bad argument");
+    if (n == 0) return RT_OK;
+    size_t need = (size_t)n * (6 * 4 + 4 + 4 + 4);
+    if (s->trace_bytes < need) {
+        if (s->d_trace) cudaFree(s->d_trace);
+        s->d_trace = nullptr;
+        s->trace_bytes = 0;
+        RT_CUDA(cudaMalloc(&s->d_trace, need));
+        s->trace_bytes = need;
+    }
+    float* d_rays = (float*)s->d_trace;
+    int* d_type = (int*)(d_rays + 6 * (size_t)n);
+    int* d_index = d_type + n;
+    float* d_t = (float*)(d_index + n);
+    RT_CUDA(cudaMemcpyAsync(d_rays, rays6, (size_t)n * 24, cudaMemcpyHostToDevice, s->stream));
+    DevScene dev = s->dev;
+    RT_CUDA(launch_trace_primary(dev, d_rays, n, tmin, tmax, d_type, d_index, d_t, s->stream));
+    RT_CUDA(cudaMemcpyAsync(type, d_type, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaMemcpyAsync(index, d_index, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaMemcpyAsync(t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaStreamSynchronize(s->stream));
+    return RT_OK;
+}
+
+int rt_tonemap_u8(rt_scene* s, const void* d_fb, int W, int H, int divisor, unsigned char* rgb) {
+    if (!s || !rgb || W <= 0 || H <= 0 || divisor <= 0) return fail(RT_ERR_INVALID, "rt_tonemap_u8: bad argument");
+    const float* src = d_fb ? (const float*)d_fb : s->d_fb;
+    if (!src) return fail(RT_ERR_INVALID, "rt_tonemap_u8: no framebuffer");
+    size_t n = (size_t)W * H * 3;
+    if (s->u8_bytes < n) {
+        if (s->d_u8) cudaFree(s->d_u8);
+        s->d_u8 = nullptr;
+        s->u8_bytes = 0;
+        RT_CUDA(cudaMalloc((void**)&s->d_u8, n));
+        s->u8_bytes = n;
+    }
+    RT_CUDA(launch_tonemap(src, n, divisor, s->d_u8, s->stream));
+    RT_CUDA(cudaMemcpyAsync(rgb, s->d_u8, n, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaStreamSynchronize(s->stream));
+    return RT_OK;
+}
+
+unsigned long long rt_tiles_packed_floats(int W, int H, int nranks) { return tiles_packed_floats(W, H, nranks < 1 ? 1 : nranks); }
+int rt_tiles_pack(rt_scene* s, const void* d_fb, int W, int H, int rank, int nranks, void* d_packed, void* stream) {
+    if (!s || !d_fb || !d_packed || nranks < 1 || rank < 0 || rank >= nranks) return fail(RT_ERR_INVALID, "rt_tiles_pack: bad argument");
+    RT_CUDA(launch_tiles_pack((const float*)d_fb, W, H, rank, nranks, (float*)d_packed, (cudaStream_t)stream));
+    return RT_OK;
+}
+int rt_tiles_unpack(rt_scene* s, const void* d_all, int W, int H, int nranks, void* d_fb, void* stream) {
+    if (!s || !d_fb || !d_all || nranks < 1) return fail(RT_ERR_INVALID, "rt_tiles_unpack: bad argument");
+    RT_CUDA(launch_tiles_unpack((const float*)d_all, W, H, nranks, (float*)d_fb, (cudaStream_t)stream));
+    return RT_OK;
+}
+
+}  // extern "C"
