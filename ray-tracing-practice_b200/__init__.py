@@ -1,0 +1,391 @@
+"""ctypes binding of librt_b200.so -- the C-ABI in include/rt_b200.h plus the host mirror (host/host_api.cpp).
+
+This package holds no compute of its own: every render / trace call goes straight into the CUDA library.  If the
+library is missing it is built in-tree with the package Makefile (nvcc, sm_100a); if that fails the import raises --
+there is no Python or CPU fallback.
+
+The directory name carries a hyphen (it is the reference's name + "_b200"), so import it through the repo-root shim:
+``import rtp_b200 as rt``.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "librt_b200.so")
+
+# numpy images of the reference PODs that cross the boundary (include/rt_b200.h)
+SPHERE = np.dtype({"names": ["center", "radius", "material_idx"], "formats": [("<f4", 3), "<f4", "<i4"],
+                   "offsets": [0, 12, 16], "itemsize": 32})
+PLANE = np.dtype({"names": ["type", "D", "material_idx", "w", "u", "v", "base", "normal"],
+                  "formats": ["<i4", "<f4", "<i4", ("<f4", 3), ("<f4", 3), ("<f4", 3), ("<f4", 3), ("<f4", 3)],
+                  "offsets": [0, 4, 8, 12, 24, 36, 48, 60], "itemsize": 80})
+MATERIAL = np.dtype({"names": ["type", "fuzz", "ir", "absorption", "albedo", "emit", "tex_obj", "cpu_tex"],
+                     "formats": ["<i4", "<f4", "<f4", ("<f4", 3), ("<f4", 3), ("<f4", 3), "<u8", "<u8"],
+                     "offsets": [0, 4, 8, 12, 24, 36, 48, 56], "itemsize": 64})
+CAMERA = np.dtype({"names": ["origin", "pixel00_loc", "pixel_delta_u", "pixel_delta_v", "background", "image_width",
+                             "image_height", "samples_per_pixel", "max_depth"],
+                   "formats": [("<f4", 3)] * 5 + ["<i4"] * 4, "offsets": [0, 12, 24, 36, 48, 60, 64, 68, 72],
+                   "itemsize": 76})
+
+LAMBERTIAN, METAL, DIELECTRIC, DIFFUSE_LIGHT = 0, 1, 2, 3
+QUAD, ELLIPSE, TRIANGLE = 0, 1, 2
+KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1
+RNG_PHILOX, RNG_REFERENCE = 0, 1
+TEX_CPU, TEX_GPU = 0, 1
+TILE = 16
+
+C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
+                 "rt_render_finish", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
+                 "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_version"]
+
+
+class RtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("rt_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class RenderOpts(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("kernel", C.c_int), ("rng", C.c_int), ("exact_math", C.c_int),
+                ("tex_mode", C.c_int), ("seed", C.c_ulonglong), ("tile_rank", C.c_int), ("tile_nranks", C.c_int),
+                ("count_work", C.c_int), ("top_nodes_in_smem", C.c_int)]
+
+
+class WorkCounters(C.Structure):
+    _fields_ = [(n, C.c_ulonglong) for n in
+                ("segments", "node_visits", "sphere_tests", "plane_tests", "shaded_hits", "samples")]
+
+
+class SceneStats(C.Structure):
+    _fields_ = [("num_spheres", C.c_int), ("num_planes", C.c_int), ("num_materials", C.c_int), ("wide_nodes", C.c_int),
+                ("wide_depth", C.c_int), ("max_stack", C.c_int), ("leaves", C.c_int), ("sah_cost", C.c_float),
+                ("build_ms", C.c_float), ("upload_ms", C.c_float), ("device_bytes", C.c_ulonglong)]
+
+
+def build(force=False):
+    """Compile librt_b200.so + rt_main in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    if force or not os.path.exists(LIB_PATH):
+        subprocess.check_call(["make", "-s", "-C", HERE] + (["-B"] if force else []))
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            build()
+        L = C.CDLL(LIB_PATH)
+        vp, ci, cf = C.c_void_p, C.c_int, C.c_float
+        L.rt_last_error.restype = C.c_char_p
+        L.rt_version.restype = C.c_char_p
+        L.rt_scene_create.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp]
+        L.rt_scene_destroy.argtypes = [vp]
+        L.rt_scene_get_stats.argtypes = [vp, vp]
+        L.rt_render.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        L.rt_render_device.argtypes = [vp, vp, vp, vp, vp]
+        L.rt_render_finish.argtypes = [vp, vp, vp, vp]
+        L.rt_trace_primary.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp]
+        L.rt_tonemap_u8.argtypes = [vp, vp, ci, ci, ci, vp]
+        L.rt_tiles_pack.argtypes = [vp, vp, ci, ci, ci, ci, vp, vp]
+        L.rt_tiles_unpack.argtypes = [vp, vp, ci, ci, ci, vp, vp]
+        L.rt_tiles_packed_floats.restype = C.c_ulonglong
+        L.rt_tiles_packed_floats.argtypes = [ci, ci, ci]
+        # host mirror
+        L.rth_scene_from_config.argtypes = [C.c_char_p, C.c_char_p, vp]
+        L.rth_scene_empty.argtypes = [vp]
+        L.rth_scene_destroy.argtypes = [vp]
+        L.rth_scene_error.restype = C.c_char_p
+        L.rth_scene_error.argtypes = [vp]
+        L.rth_scene_counts.argtypes = [vp, vp]
+        L.rth_scene_copy.argtypes = [vp, vp, vp, vp, vp]
+        L.rth_scene_add_spheres.argtypes = [vp, ci, C.c_uint]
+        L.rth_scene_params.argtypes = [vp, vp, vp]
+        L.rth_camera_for_frame.argtypes = [vp, ci, vp]
+        L.rth_build_camera.argtypes = [ci, ci, vp, vp, cf, ci, ci, vp]
+        L.rth_make_planes.argtypes = [vp, vp, vp, ci, vp]
+        L.rth_default_config.restype = C.c_char_p
+        L.rth_tonemap.argtypes = [vp, C.c_ulonglong, ci, vp]
+        L.rth_save.argtypes = [C.c_char_p, ci, ci, vp, ci]
+        L.rth_load_texels.argtypes = [C.c_char_p, vp, vp, vp]
+        L.rth_bvh_check.argtypes = [vp, ci, vp, ci, vp, vp, vp]
+        L.rth_gpu_render.argtypes = [vp, ci, C.c_char_p, ci]
+        L.rth_set_output.argtypes = [vp, C.c_char_p, ci, ci, ci, ci, ci]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RtError(rc, lib().rt_last_error().decode())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def device_count():
+    return lib().rt_device_count()
+
+
+# ------------------------------------------------------------------------------------------------ host mirror
+class HostScene:
+    """read_scene_params + create_scene (src/main.cu:346-550) on the host; arrays in the reference's layouts."""
+
+    def __init__(self, config_text=None, texture=None):
+        """texture: None keeps the config's path, "" skips the texture, a path overrides it."""
+        self.h = C.c_void_p()
+        L = lib()
+        if config_text is None:
+            L.rth_scene_empty(C.byref(self.h))
+        else:
+            rc = L.rth_scene_from_config(config_text.encode(), None if texture is None else texture.encode(),
+                                         C.byref(self.h))
+            if rc != 0:
+                msg = L.rth_scene_error(self.h).decode()
+                L.rth_scene_destroy(self.h)
+                raise ValueError(msg)
+        self.warning = L.rth_scene_error(self.h).decode()
+
+    def add_spheres(self, n, seed=1234):
+        lib().rth_scene_add_spheres(self.h, int(n), int(seed))
+        return self
+
+    def counts(self):
+        o = (C.c_int * 5)()
+        lib().rth_scene_counts(self.h, o)
+        return dict(spheres=o[0], planes=o[1], materials=o[2], tex_w=o[3], tex_h=o[4])
+
+    def arrays(self):
+        c = self.counts()
+        sp = np.zeros(c["spheres"], SPHERE)
+        pl = np.zeros(c["planes"], PLANE)
+        mt = np.zeros(c["materials"], MATERIAL)
+        tex = np.zeros((c["tex_h"], c["tex_w"], 4), np.float32) if c["tex_w"] else None
+        lib().rth_scene_copy(self.h, _ptr(sp), _ptr(pl), _ptr(mt), _ptr(tex))
+        return sp, pl, mt, tex
+
+    def params(self):
+        o = (C.c_int * 5)()
+        f = C.c_float()
+        lib().rth_scene_params(self.h, o, C.byref(f))
+        return dict(W=o[0], H=o[1], max_depth=o[2], sqrt_spp=o[3], num_frames=o[4], fov=f.value)
+
+    def set_output(self, pattern=None, num_frames=0, W=0, H=0, max_depth=0, sqrt_spp=0):
+        lib().rth_set_output(self.h, pattern.encode() if pattern else None, num_frames, W, H, max_depth, sqrt_spp)
+
+    def camera(self, frame=0):
+        cam = np.zeros(1, CAMERA)
+        lib().rth_camera_for_frame(self.h, frame, _ptr(cam))
+        return cam
+
+    def gpu_render(self, fmt=0):
+        """gpu_render(SceneParams&, SceneData&) of the reference (src/camera.cu:290) over the C-ABI. Returns the log."""
+        buf = C.create_string_buffer(1 << 16)
+        rc = lib().rth_gpu_render(self.h, fmt, buf, len(buf))
+        if rc != 0:
+            raise RtError(rc, lib().rt_last_error().decode())
+        return buf.value.decode()
+
+    def close(self):
+        if self.h:
+            lib().rth_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+def build_camera(H, W, lookfrom, lookat, vfov, spp, max_depth):
+    cam = np.zeros(1, CAMERA)
+    a = np.ascontiguousarray(lookfrom, np.float32)
+    b = np.ascontiguousarray(lookat, np.float32)
+    lib().rth_build_camera(H, W, _ptr(a), _ptr(b), float(vfov), spp, max_depth, _ptr(cam))
+    return cam
+
+
+def make_planes(base, u, v, material_idx, ptype):
+    """PlaneData host constructor (include/plane.h:19-28) for n planes."""
+    buv = np.ascontiguousarray(np.concatenate([np.asarray(base, np.float32).reshape(-1, 3),
+                                               np.asarray(u, np.float32).reshape(-1, 3),
+                                               np.asarray(v, np.float32).reshape(-1, 3)], 1), np.float32)
+    n = len(buv)
+    mat = np.ascontiguousarray(np.broadcast_to(np.asarray(material_idx, np.int32), (n,)))
+    typ = np.ascontiguousarray(np.broadcast_to(np.asarray(ptype, np.int32), (n,)))
+    out = np.zeros(n, PLANE)
+    lib().rth_make_planes(_ptr(buv), _ptr(mat), _ptr(typ), n, _ptr(out))
+    return out
+
+
+def default_config():
+    return lib().rth_default_config().decode()
+
+
+def tonemap_host(fb_sum, divisor):
+    fb = np.ascontiguousarray(fb_sum, np.float32)
+    out = np.zeros(fb.shape, np.uint8)
+    lib().rth_tonemap(_ptr(fb), fb.size, int(divisor), _ptr(out))
+    return out
+
+
+def save_image(path, rgb_u8, fmt=0):
+    rgb = np.ascontiguousarray(rgb_u8, np.uint8)
+    H, W = rgb.shape[0], rgb.shape[1]
+    return lib().rth_save(path.encode(), W, H, _ptr(rgb), fmt) == 0
+
+
+def load_texels(path):
+    w, h = C.c_int(), C.c_int()
+    if lib().rth_load_texels(path.encode(), None, C.byref(w), C.byref(h)) != 0:
+        return None
+    out = np.zeros((h.value, w.value, 4), np.float32)
+    lib().rth_load_texels(path.encode(), _ptr(out), C.byref(w), C.byref(h))
+    return out
+
+
+def bvh_check(spheres, planes):
+    sp = np.ascontiguousarray(spheres, SPHERE)
+    pl = np.ascontiguousarray(planes, PLANE)
+    o = (C.c_int * 4)()
+    sah, ms = C.c_float(), C.c_float()
+    rc = lib().rth_bvh_check(_ptr(sp), len(sp), _ptr(pl), len(pl), o, C.byref(sah), C.byref(ms))
+    return rc, dict(nodes=o[0], depth=o[1], max_stack=o[2], leaves=o[3], sah=sah.value, build_ms=ms.value)
+
+
+# ------------------------------------------------------------------------------------------------ device scene
+class Scene:
+    """rt_scene handle: the arrays create_scene produces, uploaded as wide BVH + SoA buffers (needs a GPU)."""
+
+    def __init__(self, spheres, planes, materials, tex=None, tex_material=-1):
+        self.h = C.c_void_p()
+        sp = np.ascontiguousarray(spheres, SPHERE)
+        pl = np.ascontiguousarray(planes, PLANE)
+        mt = np.ascontiguousarray(materials, MATERIAL)
+        tw = th = 0
+        if tex is not None:
+            tex = np.ascontiguousarray(tex, np.float32)
+            th, tw = tex.shape[0], tex.shape[1]
+        _check(lib().rt_scene_create(_ptr(sp), len(sp), _ptr(pl), len(pl), _ptr(mt), len(mt), _ptr(tex), tw, th,
+                                     tex_material if tex is not None else -1, C.byref(self.h)))
+
+    @classmethod
+    def from_host(cls, host):
+        sp, pl, mt, tex = host.arrays()
+        return cls(sp, pl, mt, tex, 0)
+
+    def stats(self):
+        s = SceneStats()
+        _check(lib().rt_scene_get_stats(self.h, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in SceneStats._fields_}
+
+    @staticmethod
+    def _opts(kernel=KERNEL_MEGA, rng=RNG_PHILOX, exact=False, tex_mode=TEX_GPU, seed=0, tile_rank=0, tile_nranks=1,
+              count_work=False, top_nodes=-1):
+        o = RenderOpts()
+        o.struct_size = C.sizeof(RenderOpts)
+        o.kernel, o.rng, o.exact_math, o.tex_mode, o.seed = kernel, rng, int(exact), tex_mode, seed
+        o.tile_rank, o.tile_nranks, o.count_work, o.top_nodes_in_smem = tile_rank, tile_nranks, int(count_work), top_nodes
+        return o
+
+    def render(self, cam, out=None, **kw):
+        """One frame through rt_render (host framebuffer). Returns (sum image [H,W,3], info dict)."""
+        cam = np.ascontiguousarray(cam, CAMERA)
+        W, H = int(cam["image_width"][0]), int(cam["image_height"][0])
+        fb = out if out is not None else np.zeros((H, W, 3), np.float32)
+        o = self._opts(**kw)
+        segs, ms, wc = C.c_ulonglong(), C.c_float(), WorkCounters()
+        _check(lib().rt_render(self.h, _ptr(cam), C.byref(o), _ptr(fb), C.byref(segs), C.byref(ms), C.byref(wc)))
+        info = {n: getattr(wc, n) for n, _ in WorkCounters._fields_}
+        info.update(segments=segs.value, kernel_ms=ms.value)
+        return fb, info
+
+    def render_device(self, cam, d_fb_ptr, stream=None, **kw):
+        cam = np.ascontiguousarray(cam, CAMERA)
+        o = self._opts(**kw)
+        _check(lib().rt_render_device(self.h, _ptr(cam), C.byref(o), C.c_void_p(d_fb_ptr), C.c_void_p(stream or 0)))
+
+    def finish(self):
+        segs, ms, wc = C.c_ulonglong(), C.c_float(), WorkCounters()
+        _check(lib().rt_render_finish(self.h, C.byref(segs), C.byref(ms), C.byref(wc)))
+        info = {n: getattr(wc, n) for n, _ in WorkCounters._fields_}
+        info.update(segments=segs.value, kernel_ms=ms.value)
+        return info
+
+    def trace_primary(self, rays6, tmin=0.001, tmax=1e30):
+        rays = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = len(rays)
+        typ, idx, t = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float32)
+        _check(lib().rt_trace_primary(self.h, _ptr(rays), n, tmin, tmax, _ptr(typ), _ptr(idx), _ptr(t)))
+        return typ, idx, t
+
+    def tonemap_u8(self, W, H, divisor, d_fb_ptr=None):
+        out = np.zeros((H, W, 3), np.uint8)
+        _check(lib().rt_tonemap_u8(self.h, C.c_void_p(d_fb_ptr or 0), W, H, divisor, _ptr(out)))
+        return out
+
+    def tiles_pack(self, d_fb_ptr, W, H, rank, nranks, d_packed_ptr, stream=None):
+        _check(lib().rt_tiles_pack(self.h, C.c_void_p(d_fb_ptr), W, H, rank, nranks, C.c_void_p(d_packed_ptr),
+                                   C.c_void_p(stream or 0)))
+
+    def tiles_unpack(self, d_all_ptr, W, H, nranks, d_fb_ptr, stream=None):
+        _check(lib().rt_tiles_unpack(self.h, C.c_void_p(d_all_ptr), W, H, nranks, C.c_void_p(d_fb_ptr),
+                                     C.c_void_p(stream or 0)))
+
+    def close(self):
+        if self.h:
+            lib().rt_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+def tiles_packed_floats(W, H, nranks):
+    return int(lib().rt_tiles_packed_floats(W, H, nranks))
+
+
+def pixel_center_rays(cam):
+    """Rays through the pixel centres of a CameraData (no jitter): N x 6 float32, row-major pixels."""
+    c = np.ascontiguousarray(cam, CAMERA)[0]
+    W, H = int(c["image_width"]), int(c["image_height"])
+    ii, jj = np.meshgrid(np.arange(W, dtype=np.float32), np.arange(H, dtype=np.float32))
+    p = (c["pixel00_loc"] + ii[..., None] * c["pixel_delta_u"]) + jj[..., None] * c["pixel_delta_v"]
+    d = (p - c["origin"]).astype(np.float32)
+    o = np.broadcast_to(c["origin"], d.shape)
+    return np.ascontiguousarray(np.concatenate([o, d], -1).reshape(-1, 6), np.float32)
+
+
+# ------------------------------------------------------------------------------------------------ configs
+def test_config_text(W=200, H=100, fov=90, max_depth=5, sqrt_spp=2, texture="../floor2.jpg", output="test_output_%d.png",
+                     num_frames=1):
+    """The config create_test_config.py prints (create_test_config.py:4-79): the shipped 3-solid scene with a STATIC
+    camera at (15 cos 3.14159, 15 sin 3.14159, 4.5) looking at (0,0,4.5).  Same token order as the reference format."""
+    lines = [str(num_frames), output, "%d %d %g" % (W, H, fov),
+             "15.0 4.5 3.14159", "0.0 0.0", "0.0 0.0 0.0", "0.0 0.0",
+             "0.0 4.5 0.0", "0.0 0.0", "0.0 0.0 0.0", "0.0 0.0",
+             "0.0 0.0 3.0", "0.3 0.0 0.0", "3.0", "1.5 0.1", "3",
+             "4.0 0.0 6.0", "0.0 0.3 0.0", "3.0", "1.2 0.1", "2",
+             "8.0 0.0 9.0", "0.0 0.0 0.3", "3.0", "1.0 0.1", "1",
+             "-15.0 -15.0 -1.0", "-15.0 15.0 -1.0", "15.0 15.0 -1.0", "15.0 -15.0 -1.0",
+             texture, "1.0 1.0 1.0", "0.3", "4",
+             "-15.0 -15.0 10.0", "10.0 10.0 10.0", "-15.0 15.0 10.0", "10.0 10.0 10.0",
+             "15.0 15.0 10.0", "10.0 10.0 10.0", "15.0 -15.0 10.0", "10.0 10.0 10.0",
+             "%d %d" % (max_depth, sqrt_spp)]
+    return "\n".join(lines) + "\n"
+
+
+# the synthetic configs of BASELINE.json: create_test_config.py scene + N seeded spheres
+CONFIGS = {
+    "test_config_200x100": dict(n=0, W=200, H=100, sqrt_spp=2, depth=5),
+    "spheres10k_1080p_64spp_d16": dict(n=10000, W=1920, H=1080, sqrt_spp=8, depth=16),
+    "spheres100k_1080p_256spp_d32": dict(n=100000, W=1920, H=1080, sqrt_spp=16, depth=32),
+    "spheres1m_4k_64spp_d8": dict(n=1000000, W=3840, H=2160, sqrt_spp=8, depth=8),
+    "spheres100k_8k_1024spp_d32": dict(n=100000, W=7680, H=4320, sqrt_spp=32, depth=32),
+}
+
+
+def synthetic_scene(n_spheres, W=1920, H=1080, sqrt_spp=8, depth=16, seed=1234, texture=""):
+    """HostScene of the test-config scene + n seeded spheres (mt19937(seed)); texture "" = untextured floor."""
+    hs = HostScene(test_config_text(W, H, 90, depth, sqrt_spp), texture=texture)
+    if n_spheres > 0:
+        hs.add_spheres(n_spheres, seed)
+    return hs

@@ -1,0 +1,35 @@
+// rt_main.cpp -- drop-in for the reference executable (src/main.cu:572-606): `rt_main [--gpu|--default] < config`.
+// `--cpu` is refused: this build has no CPU render path (the reference's --cpu lives on as oracle/_ref).
+// Extensions (all optional, after the mode): --png | --ppm choose the saver the reference ships but never wires up;
+// --spheres N [--seed S] appends the seeded N-sphere field of BASELINE.json's configs 2-4.
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <string>
+
+#include "scene_host.h"
+
+int main(int argc, char** argv) {
+    using namespace rtb;
+    int format = 0, spheres = 0;
+    unsigned seed = 1234;
+    bool want_default = false;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        if (a == "--default") want_default = true;
+        else if (a == "--gpu") {}
+        else if (a == "--cpu") { std::cerr << "rt_main: no CPU render path in this build (use the reference's --cpu)\n"; return 2; }
+        else if (a == "--png") format = 1;
+        else if (a == "--ppm") format = 2;
+        else if (a == "--spheres" && i + 1 < argc) spheres = std::atoi(argv[++i]);
+        else if (a == "--seed" && i + 1 < argc) seed = (unsigned)std::strtoul(argv[++i], nullptr, 10);
+    }
+    if (want_default) { std::cout << default_config_text(); return 0; }
+    SceneParams params = read_scene_params(std::cin);
+    HostScene scene;
+    std::string err;
+    if (!create_scene(params, scene, true, &err)) { std::cerr << err << std::endl; return 1; }
+    if (!err.empty()) std::cerr << err << std::endl;
+    if (spheres > 0) make_synthetic_spheres(scene, spheres, seed);
+    return gpu_render(params, scene, format, std::cout);
+}

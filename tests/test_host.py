@@ -1,0 +1,180 @@
+"""Host-side logic of the drop-in (no GPU needed): config parser, scene assembly, camera path, savers, wide-BVH builder,
+and the C-ABI library's symbol table / error behaviour without a device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+from conftest import ROOT, bits, golden, has_gpu
+
+
+def field_equal(a, b, names):
+    for n in names:
+        if a[n].dtype.kind == "f":
+            if not (a[n].view(np.uint32) == b[n].view(np.uint32)).all():
+                return False
+        elif not (a[n] == b[n]).all():
+            return False
+    return True
+
+
+def test_c_abi_exports_every_declared_symbol(rt):
+    hdr = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"rt_scene", "rt_render_opts", "rt_work_counters", "rt_scene_stats"}
+    assert declared == set(rt.C_ABI_SYMBOLS), declared ^ set(rt.C_ABI_SYMBOLS)
+    L = C.CDLL(rt.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in rt.lib().rt_version()
+
+
+def test_struct_sizes_match_header(rt):
+    assert C.sizeof(rt.RenderOpts) == 48 and C.sizeof(rt.WorkCounters) == 48
+    assert rt.SPHERE.itemsize == 32 and rt.PLANE.itemsize == 80 and rt.MATERIAL.itemsize == 64 and rt.CAMERA.itemsize == 76
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the behaviour WITHOUT a device")
+def test_no_cpu_fallback_without_device(rt):
+    g = golden("test_config_frame.npz")
+    with pytest.raises(rt.RtError) as e:
+        rt.Scene(g["spheres"], g["planes"], g["materials"])
+    assert e.value.code == 3 and "no CUDA device" in str(e.value)  # RT_ERR_NO_DEVICE
+
+
+def test_argument_validation(rt):
+    g = golden("test_config_frame.npz")
+    sp = g["spheres"].copy()
+    sp["material_idx"][0] = 999
+    with pytest.raises(rt.RtError) as e:
+        rt.Scene(sp, g["planes"], g["materials"])
+    assert e.value.code == 1
+    pl = g["planes"].copy()
+    pl["type"][0] = 7
+    with pytest.raises(rt.RtError) as e:
+        rt.Scene(g["spheres"], pl, g["materials"])
+    assert e.value.code == 1
+
+
+def test_default_config_and_parser(rt):
+    cfg = rt.default_config()
+    hs = rt.HostScene(cfg, texture="")
+    assert hs.params() == dict(W=1080, H=720, max_depth=50, sqrt_spp=50, num_frames=100, fov=50.0)
+    assert hs.counts()["spheres"] == 94 and hs.counts()["planes"] == 105 and hs.counts()["materials"] == 12
+    if os.path.exists("/root/reference/config.txt"):
+        assert cfg.split() == open("/root/reference/config.txt").read().split()
+    # lights are clamped to 4 (src/main.cu:538-540); zero lights is rejected (create_scene reads lights[0])
+    five = cfg.replace("\n4\n", "\n5\n").replace("15.0 -15.0 1   10.0 10.0 10.0\n", "15.0 -15.0 1   10.0 10.0 10.0\n0 0 30 1 1 1\n")
+    assert rt.HostScene(five, texture="").counts()["spheres"] == 94
+    none = cfg.replace("\n4\n-15.0 -15.0 1  10.0 10.0 10.0\n-15.0 15.0 1   10.0 10.0 10.0\n15.0 15.0 1    10.0 10.0 10.0\n15.0 -15.0 1   10.0 10.0 10.0\n", "\n0\n")
+    with pytest.raises(ValueError):
+        rt.HostScene(none, texture="")
+
+
+def test_scene_assembly_matches_reference_fixture(rt):
+    s = golden("shipped_scene.npz")
+    hs = rt.HostScene(rt.default_config(), texture="")
+    sp, pl, mt, _ = hs.arrays()
+    assert field_equal(sp, s["spheres"], sp.dtype.names)
+    assert field_equal(pl, s["planes"], pl.dtype.names)
+    used = {0: ["albedo"], 1: ["albedo", "fuzz"], 2: ["ir", "absorption"], 3: ["emit"]}
+    for a, b in zip(mt, s["materials"]):
+        assert a["type"] == b["type"]
+        for n in used[int(a["type"])]:
+            assert (np.asarray(a[n]).view(np.uint32) == np.asarray(b[n]).view(np.uint32)).all()
+    # material order is parity-relevant: floor METAL, edge light, then (glass, border) x3, then 4 lights
+    assert list(mt["type"]) == [1, 3, 2, 1, 2, 1, 2, 1, 3, 3, 3, 3]
+
+
+def test_texture_decode_matches_reference(rt):
+    path = "/root/reference/floor.jpg"
+    if not os.path.exists(path):
+        pytest.skip("floor.jpg lives in /root/reference")
+    s = golden("shipped_scene.npz")
+    tex = rt.load_texels(path)
+    assert list(tex.shape) == list(s["tex_shape"]) == [1330, 2000, 4]
+    assert np.float64(tex.astype(np.float64).sum()) == s["tex_checksum"][0]
+    assert tex[:4, :4].tobytes() == s["tex_corner"].tobytes() and tex[::133, ::200].tobytes() == s["tex_probe"].tobytes()
+
+
+def test_test_config_text_is_the_reference_scripts_output(rt):
+    g = golden("test_config_frame.npz")
+    assert rt.test_config_text() == str(g["config"])
+    hs = rt.HostScene(str(g["config"]), texture="")
+    sp, pl, mt, _ = hs.arrays()
+    assert field_equal(sp, g["spheres"], sp.dtype.names) and field_equal(pl, g["planes"], pl.dtype.names)
+    assert hs.camera(0).tobytes() == g["camera"].tobytes()
+
+
+def test_camera_path_and_saver_reproduce_the_reference_program(rt, orc, tmp_path):
+    """3 frames on the moving camera path, as written by the reference's own cpu_render + BinarySaver
+    (program_frames.npz): host-mirror camera_for_frame -> oracle frame -> host tonemap -> bytes must be identical."""
+    g = golden("program_frames.npz")
+    hs = rt.HostScene(str(g["config"]).replace("OUTDIR", str(tmp_path)), texture="")
+    sp, pl, mt, _ = hs.arrays()
+    p = hs.params()
+    sc = orc.scene(sp, pl, mt)
+    for n in range(3):
+        cam = hs.camera(n)
+        fb, _ = sc.render(cam, hit_mode=1)
+        rgb = rt.tonemap_host(fb, p["sqrt_spp"])  # the reference divides by sqrt_spp, not spp (Q1)
+        path = str(tmp_path / ("f_%d.bin" % n))
+        assert rt.save_image(path, rgb, 0)
+        assert np.fromfile(path, np.uint8).tobytes() == g["frames"][n].tobytes()
+    hdr = np.frombuffer(g["frames"][0][:8].tobytes(), np.int32)
+    assert list(hdr) == [48, 32]
+
+
+def test_savers(rt, tmp_path):
+    rgb = (np.arange(6 * 4 * 3) % 251).astype(np.uint8).reshape(4, 6, 3)
+    assert rt.save_image(str(tmp_path / "a.ppm"), rgb, 2)
+    txt = open(tmp_path / "a.ppm").read().split()
+    assert txt[:4] == ["P3", "6", "4", "255"] and [int(x) for x in txt[4:]] == list(rgb.reshape(-1))
+    assert rt.save_image(str(tmp_path / "a.png"), rgb, 1)
+    assert open(tmp_path / "a.png", "rb").read(8) == b"\x89PNG\r\n\x1a\n"
+    fb = np.array([[[0.0, 4.0, 16.0]], [[1e9, 0.25, 2.0]]], np.float32)
+    out = rt.tonemap_host(fb, 4)
+    want = [int(256 * min(max(np.sqrt(np.float32(v) * np.float32(0.25)), 0), np.float32(0.999))) for v in fb.reshape(-1)]
+    assert list(out.reshape(-1)) == want
+
+
+def test_synthetic_generator_is_seeded_and_matches_fixture(rt):
+    g = golden("synthetic2k_textured.npz")
+    a = rt.synthetic_scene(2000, seed=1234).arrays()
+    b = rt.synthetic_scene(2000, seed=1234).arrays()
+    c = rt.synthetic_scene(2000, seed=99).arrays()
+    assert a[0].tobytes() == b[0].tobytes() and a[0].tobytes() != c[0].tobytes()
+    assert len(a[0]) == 2094 and len(a[2]) == 12 + 64
+    assert field_equal(a[0][::97], g["sphere_probe"], a[0].dtype.names)
+    r = 0.45 * 30 / np.sqrt(2000)
+    s = a[0][94:]
+    assert s["radius"].min() >= 0.5 * r * 0.999 and s["radius"].max() <= r * 1.001
+    assert np.abs(s["center"][:, :2]).max() <= 15 and s["center"][:, 2].min() >= -1 + r * 0.999
+    types = a[2]["type"][12:]
+    assert [(types == t).sum() for t in range(4)] == [38, 13, 10, 3]
+
+
+@pytest.mark.parametrize("n", [0, 1, 5, 3000, 60000])
+def test_wide_bvh_is_structurally_sound(rt, n):
+    hs = rt.synthetic_scene(n) if n != 1 else None
+    if n == 1:
+        sp = np.zeros(1, rt.SPHERE)
+        sp["radius"] = 1
+        rc, st = rt.bvh_check(sp, np.zeros(0, rt.PLANE))
+    else:
+        sp, pl, _, _ = hs.arrays()
+        rc, st = rt.bvh_check(sp, pl)
+    assert rc == 0, (rc, st)
+    assert st["max_stack"] <= 64 and st["depth"] <= 40
+    if n >= 3000:
+        assert st["leaves"] <= (n + 199) and st["nodes"] < n
+
+
+def test_wide_bvh_degenerate_inputs(rt):
+    sp = np.zeros(500, rt.SPHERE)  # 500 coincident spheres: no spatial split exists
+    sp["radius"] = 0.5
+    rc, st = rt.bvh_check(sp, np.zeros(0, rt.PLANE))
+    assert rc == 0 and st["leaves"] >= 125
+    rc, st = rt.bvh_check(np.zeros(0, rt.SPHERE), np.zeros(0, rt.PLANE))
+    assert rc == 0 and st["nodes"] == 1
