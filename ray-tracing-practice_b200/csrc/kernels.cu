@@ -13,26 +13,17 @@
 //     once, so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
 #include "path.cuh"
+#include "smem_top.cuh"
 
 namespace rtb {
-
-// stage the top of the BVH: wide nodes [0, top) -> shared memory, 9 x float4 stride
-__device__ __forceinline__ void stage_top_nodes(const DevScene& sc, float4* s_top) {
-    int n4 = sc.top_nodes * 8;
-    for (int i = threadIdx.x; i < n4; i += blockDim.x) {
-        int node = i >> 3, k = i & 7;
-        s_top[node * kTopStride + k] = __ldg(sc.nodes + i);
-    }
-    __syncthreads();
-}
 
 template <int MODE, bool X, bool COUNT>
 __global__ void __launch_bounds__(256, 2) render_mega(const __grid_constant__ DevScene sc, const __grid_constant__ FrameParams fp) {
     extern __shared__ float4 smem4[];
-    float4* s_top = smem4;
-    float* s_st = reinterpret_cast<float*>(smem4 + sc.top_nodes * kTopStride);
-    int* s_sr = reinterpret_cast<int*>(s_st + kSmemStack * blockDim.x);
-    stage_top_nodes(sc, s_top);
+    const TraversalSmem ts = carve_and_stage(sc, smem4);
+    const float4* s_top = ts.top;
+    float* s_st = ts.st;
+    int* s_sr = ts.sr;
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -72,7 +63,10 @@ __global__ void __launch_bounds__(256, 2) render_mega(const __grid_constant__ De
                 int blk = q >> 5;  // 8 blocks of 8x4 pixels inside the 16x16 tile
                 int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
                 int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
-                if (x < W && y < H) {
+                if (x < W && y < H && (spp <= 0 || fp.cam.depth <= 0)) {
+                    float* out = fp.fb + 3 * ((size_t)y * W + x);  // no samples / no segments: the pixel is black
+                    out[0] = 0.f; out[1] = 0.f; out[2] = 0.f;
+                } else if (x < W && y < H) {
                     has_pixel = true;
                     px = x; py = y;
                     sample = 0;
@@ -153,10 +147,10 @@ __global__ void __launch_bounds__(256, 2) trace_primary_kernel(const __grid_cons
                                                                int n, float tmin, float tmax, int* __restrict__ type,
                                                                int* __restrict__ index, float* __restrict__ t) {
     extern __shared__ float4 smem4[];
-    float4* s_top = smem4;
-    float* s_st = reinterpret_cast<float*>(smem4 + sc.top_nodes * kTopStride);
-    int* s_sr = reinterpret_cast<int*>(s_st + kSmemStack * blockDim.x);
-    stage_top_nodes(sc, s_top);
+    const TraversalSmem ts = carve_and_stage(sc, smem4);
+    const float4* s_top = ts.top;
+    float* s_st = ts.st;
+    int* s_sr = ts.sr;
     WorkCount wc = {0, 0, 0, 0, 0, 0};
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float* r = rays6 + 6 * (size_t)i;

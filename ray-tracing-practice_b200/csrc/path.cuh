@@ -41,12 +41,11 @@ __device__ __forceinline__ void begin_path(const CameraPod& c, int x, int y, int
 // the reference's per-pixel seed base: wang_hash(i*W + j) with i = x (src/camera.cu:25)
 __device__ __forceinline__ uint32_t pixel_seed_base(int x, int y, int W) { return wang_hash_u32((uint32_t)x * (uint32_t)W + (uint32_t)y); }
 
-// one segment: closest hit, emission, scatter.  Returns true when the sample is finished (ps.L is its radiance).
+// second half of a segment, given its closest hit: miss -> background, else emission + scatter.
+// Returns true when the sample is finished (ps.L is its radiance).
 template <int MODE, bool X, bool COUNT>
-__device__ __forceinline__ bool advance_path(const DevScene& sc, const CameraPod& cam, int tex_mode, const float4* s_top, float* s_st,
-                                             int* s_sr, PathState& ps, Rng<MODE>& rng, WorkCount& wc) {
-    HitInfo hit;
-    trace_closest<X, COUNT>(sc, s_top, s_st, s_sr, ps.o, ps.d, 0.001f, 1e30f, hit, wc);  // Interval(0.001f,1e30f), camera.cu:226
+__device__ __forceinline__ bool finish_segment(const DevScene& sc, const CameraPod& cam, int tex_mode, const HitInfo& hit, PathState& ps,
+                                               Rng<MODE>& rng, WorkCount& wc) {
     wc.segments++;
     bool alive;
     if (hit.type < 0) {
@@ -59,6 +58,15 @@ __device__ __forceinline__ bool advance_path(const DevScene& sc, const CameraPod
     }
     ++ps.depth;
     return !alive || ps.depth >= cam.depth;
+}
+
+// one whole segment: closest hit (Interval(0.001f, 1e30f), src/camera.cu:226), then finish_segment
+template <int MODE, bool X, bool COUNT>
+__device__ __forceinline__ bool advance_path(const DevScene& sc, const CameraPod& cam, int tex_mode, const float4* s_top, float* s_st,
+                                             int* s_sr, PathState& ps, Rng<MODE>& rng, WorkCount& wc) {
+    HitInfo hit;
+    trace_closest<X, COUNT>(sc, s_top, s_st, s_sr, ps.o, ps.d, 0.001f, 1e30f, hit, wc);
+    return finish_segment<MODE, X, COUNT>(sc, cam, tex_mode, hit, ps, rng, wc);
 }
 
 }  // namespace rtb
