@@ -3,14 +3,20 @@
 // render_mega replaces the reference's render_kernel + ray_color (src/camera.cu:17-34, 218-252).  The reference
 // maps one thread to one pixel and runs its whole spp x depth loop nest there, so a warp lives as long as its
 // slowest pixel and dead lanes idle through every bounce.  Here the kernel is PERSISTENT (one grid sized to the
-// machine: SMs x resident CTAs) and every loop iteration advances every lane by exactly one path segment:
-//   * a lane whose path ended regenerates the next sample of ITS pixel in the same iteration, so lanes never idle
-//     on path-length variance (62 % of paths end at the first vertex, the tail runs to max_depth);
-//   * a lane whose pixel is complete takes the next pixel of its warp's 16x16 tile; a warp whose tile is used up
-//     fetches the next tile id with ONE atomicAdd (lane 0) and a shuffle broadcast -- work fetch is
-//     warp-aggregated, ballot/popc ranks hand the pixels of the tile to the lanes that need one;
-//   * per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored
-//     once, so the output is deterministic and, in parity mode, comparable bit for bit.
+// machine: SMs x resident CTAs) and a warp is a scheduler over 32 independent path states.  Every lane is in one of
+// four states -- inner node pending, leaf pending, hit ready to shade / new path wanted, idle -- and each loop
+// iteration the warp votes (ballot/popc) on which kind of step to execute:
+//   * SHADE when enough lanes have finished their segment (or nothing else can run): emission + scatter of the hit,
+//     the next sample of the lane's pixel when the path ended, the next pixel when the pixel is complete.  Lanes never
+//     wait for the longest path or the longest traversal of their warp; they wait at most until `shade_min` lanes
+//     have gathered, so the divergent shading code always runs with a useful number of lanes;
+//   * LEAF when enough lanes hold a leaf (or no lane holds an inner node): the primitive tests run together instead
+//     of once per lane inside a divergent branch of the node loop;
+//   * INNER for every lane that holds an inner node: the hot, branch-free part, executed by most lanes every iteration.
+//   Pixels come from 16x16 tiles: a warp whose tile is used up fetches the next tile id with ONE atomicAdd (lane 0)
+//   and a shuffle broadcast -- work fetch is warp-aggregated, ballot/popc ranks hand the pixels to the lanes that
+//   need one.  Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and
+//   stored once, so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
 #include "path.cuh"
 #include "smem_top.cuh"
@@ -18,88 +24,120 @@
 namespace rtb {
 
 template <int MODE, bool X, bool COUNT>
-__global__ void __launch_bounds__(256, 2) render_mega(const __grid_constant__ DevScene sc, const __grid_constant__ FrameParams fp) {
+__global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(const __grid_constant__ DevScene sc,
+                                                                                const __grid_constant__ FrameParams fp) {
     extern __shared__ float4 smem4[];
     const TraversalSmem ts = carve_and_stage(sc, smem4);
     const float4* s_top = ts.top;
-    float* s_st = ts.st;
-    int* s_sr = ts.sr;
+    float lst[kLocalStack];
+    int lsr[kLocalStack];
+    TravStack stk;
+    stk.st = ts.st; stk.sr = ts.sr; stk.lt = lst; stk.lr = lsr;
+    stk.tid = threadIdx.x; stk.nt = blockDim.x;
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int W = fp.cam.W, H = fp.cam.H, spp = fp.cam.spp;
+    const int shade_min = fp.shade_min, leaf_min = fp.leaf_min;
 
     // warp-uniform tile pool
     int pool_tile = 0, pool_next = kTile * kTile;
     bool exhausted = false;
 
-    // per-lane path state
+    // per-lane state
+    RayTrav rt;
+    trav_begin<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
+    rt.ref = kRefNeed;
     bool has_pixel = false;
     int px = 0, py = 0, sample = 0;
     PathState ps;
     ps.o = mk3(0, 0, 0); ps.d = mk3(0, 0, 1); ps.beta = mk3(1, 1, 1); ps.L = mk3(0, 0, 0); ps.depth = 0;
     V3 acc = mk3(0, 0, 0);
     Rng<MODE> rng;
+    rng.begin_sample(0u, 0u, 0u, fp.key);
     uint32_t pixel_base = 0;
-    bool new_sample = false;
     WorkCount wc = {0, 0, 0, 0, 0, 0};
 
     for (;;) {
-        // ---- 1. hand out pixels to lanes that have none (warp-aggregated fetch)
-        unsigned need = __ballot_sync(full, !has_pixel);
-        while (need && !exhausted) {
-            if (pool_next >= kTile * kTile) {
-                unsigned k = 0;
-                if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
-                k = __shfl_sync(full, k, 0);
-                if ((int)k >= fp.my_tiles) { exhausted = true; break; }
-                pool_tile = (int)k * fp.tile_nranks + fp.tile_rank;
-                pool_next = 0;
-            }
-            int avail = kTile * kTile - pool_next;
-            int rank = __popc(need & ((1u << lane) - 1u));
-            if (!has_pixel && rank < avail) {
-                int q = pool_next + rank;
-                int blk = q >> 5;  // 8 blocks of 8x4 pixels inside the 16x16 tile
-                int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
-                int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
-                if (x < W && y < H && (spp <= 0 || fp.cam.depth <= 0)) {
-                    float* out = fp.fb + 3 * ((size_t)y * W + x);  // no samples / no segments: the pixel is black
-                    out[0] = 0.f; out[1] = 0.f; out[2] = 0.f;
-                } else if (x < W && y < H) {
-                    has_pixel = true;
-                    px = x; py = y;
-                    sample = 0;
-                    acc = mk3(0, 0, 0);
-                    new_sample = true;
-                    pixel_base = pixel_seed_base(x, y, W);
+        const unsigned smask = __ballot_sync(full, rt.ref == kRefDone || rt.ref == kRefNeed);
+        const unsigned tmask = __ballot_sync(full, ref_is_leaf(rt.ref) || ref_is_inner(rt.ref));
+        if (smask == 0u && tmask == 0u) break;  // every lane idle
+        if (smask != 0u && (__popc(smask) >= shade_min || tmask == 0u)) {
+            // ---- SHADE 1: second half of the finished segments (miss -> background, else emission + scatter)
+            bool start_ray = false;
+            if (rt.ref == kRefDone) {
+                if (MODE == kRngPhilox) rng.begin_sample(pixel_base, (uint32_t)sample, (uint32_t)(py * W + px), fp.key);
+                if (finish_segment<MODE, X, COUNT>(sc, fp.cam, fp.tex_mode, trav_hit(rt), ps, rng, wc)) {
+                    // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
+                    acc = add3<X>(acc, ps.L);
+                    ++sample;
+                    if (sample >= spp) {
+                        float* out = fp.fb + 3 * ((size_t)py * W + px);
+                        out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
+                        has_pixel = false;
+                    }
+                    rt.ref = kRefNeed;
+                } else {
+                    start_ray = true;
                 }
             }
-            int n_need = __popc(need);
-            pool_next += n_need < avail ? n_need : avail;
-            need = __ballot_sync(full, !has_pixel);
+            // ---- SHADE 2: hand out pixels to lanes that have none (warp-aggregated fetch)
+            unsigned need = __ballot_sync(full, rt.ref == kRefNeed && !has_pixel);
+            while (need && !exhausted) {
+                if (pool_next >= kTile * kTile) {
+                    unsigned k = 0;
+                    if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
+                    k = __shfl_sync(full, k, 0);
+                    if ((int)k >= fp.my_tiles) { exhausted = true; break; }
+                    pool_tile = (int)k * fp.tile_nranks + fp.tile_rank;
+                    pool_next = 0;
+                }
+                int avail = kTile * kTile - pool_next;
+                int rank = __popc(need & ((1u << lane) - 1u));
+                if (rt.ref == kRefNeed && !has_pixel && rank < avail) {
+                    int q = pool_next + rank;
+                    int blk = q >> 5;  // 8 blocks of 8x4 pixels inside the 16x16 tile
+                    int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
+                    int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
+                    if (x < W && y < H && (spp <= 0 || fp.cam.depth <= 0)) {
+                        float* out = fp.fb + 3 * ((size_t)y * W + x);  // no samples / no segments: the pixel is black
+                        out[0] = 0.f; out[1] = 0.f; out[2] = 0.f;
+                    } else if (x < W && y < H) {
+                        has_pixel = true;
+                        px = x; py = y;
+                        sample = 0;
+                        acc = mk3(0, 0, 0);
+                        pixel_base = pixel_seed_base(x, y, W);
+                    }
+                }
+                int n_need = __popc(need);
+                pool_next += n_need < avail ? n_need : avail;
+                need = __ballot_sync(full, rt.ref == kRefNeed && !has_pixel);
+            }
+            // ---- SHADE 3: start the next sample of the lane's pixel; lanes left without a pixel retire
+            if (rt.ref == kRefNeed) {
+                if (has_pixel) {
+                    begin_path<MODE, X>(fp.cam, px, py, sample, pixel_base, fp.key, rng, ps);
+                    if (COUNT) wc.samples++;
+                    start_ray = true;
+                } else {
+                    rt.ref = kRefIdle;
+                }
+            }
+            if (start_ray) trav_begin<X>(rt, ps.o, ps.d, 0.001f, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
         }
-        if (!__any_sync(full, has_pixel)) break;
-
-        if (has_pixel) {
-            // ---- 2. start a sample
-            if (new_sample) {
-                begin_path<MODE, X>(fp.cam, px, py, sample, pixel_base, fp.key, rng, ps);
-                new_sample = false;
-                if (COUNT) wc.samples++;
+        // ---- LEAF: primitive tests, when enough lanes hold a leaf or no lane has an inner node to visit
+        const unsigned lmask = __ballot_sync(full, ref_is_leaf(rt.ref));
+        const unsigned imask = __ballot_sync(full, ref_is_inner(rt.ref));
+        if (lmask != 0u && (__popc(lmask) >= leaf_min || imask == 0u)) {
+            if (ref_is_leaf(rt.ref)) {
+                trav_leaf<X, COUNT>(sc, rt, wc);
+                trav_pop(rt, stk);
             }
-            // ---- 3. one path segment
-            if (advance_path<MODE, X, COUNT>(sc, fp.cam, fp.tex_mode, s_top, s_st, s_sr, ps, rng, wc)) {
-                // ---- 4. sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
-                acc = add3<X>(acc, ps.L);
-                ++sample;
-                new_sample = true;
-                if (sample >= spp) {
-                    float* out = fp.fb + 3 * ((size_t)py * W + px);
-                    out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
-                    has_pixel = false;
-                }
-            }
+        }
+        // ---- INNER: one wide node for every lane that holds one
+        if (ref_is_inner(rt.ref)) {
+            if (trav_inner<X, COUNT>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
         }
     }
 

@@ -13,6 +13,7 @@ struct FrameParams {
     int tex_mode;       // 0 cpu semantics, 1 texture unit
     int tile_rank, tile_nranks;
     int tiles_x, tiles_y, my_tiles;
+    int shade_min, leaf_min;          // megakernel scheduling thresholds (lanes), see kernels.cu
     float* fb;                        // W*H*3 sums
     unsigned int* tile_counter;       // work queue head (zeroed before launch)
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
@@ -25,6 +26,10 @@ struct LaunchCfg {
 };
 
 constexpr int kTile = 16;  // == RT_TILE
+constexpr int kMegaThreads = 256;
+constexpr int kMegaBlocksPerSM = 2;
+constexpr int kShadeMinDefault = 24;
+constexpr int kLeafMinDefault = 8;
 
 // persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1
 cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,

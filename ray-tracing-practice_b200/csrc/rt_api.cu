@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -274,7 +275,14 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     if (top > dev.num_nodes) top = dev.num_nodes;
     if (top > 1024) top = 1024;
     dev.top_nodes = top;
-    LaunchCfg cfg{s->num_sms, 2, 256};
+    LaunchCfg cfg{s->num_sms, kMegaBlocksPerSM, kMegaThreads};
+    // scheduling thresholds of the megakernel; RTB_SHADE_MIN / RTB_LEAF_MIN are tuning knobs for profiling runs
+    fp.shade_min = kShadeMinDefault;
+    fp.leaf_min = kLeafMinDefault;
+    if (const char* e = getenv("RTB_SHADE_MIN")) fp.shade_min = atoi(e);
+    if (const char* e = getenv("RTB_LEAF_MIN")) fp.leaf_min = atoi(e);
+    if (fp.shade_min < 1) fp.shade_min = 1;
+    if (fp.leaf_min < 1) fp.leaf_min = 1;
     RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, 64, stream));
     RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
     RT_CUDA(cudaEventRecord(s->ev0, stream));

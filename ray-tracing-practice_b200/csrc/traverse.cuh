@@ -112,136 +112,197 @@ __device__ __forceinline__ bool plane_t(V3 o, V3 d, const float4* __restrict__ p
 }
 
 // ---- traversal ----------------------------------------------------------------------------------------------
-struct Stack {
-    float* st;  // shared: [kSmemStack][blockDim] distances
-    int* sr;    // shared: [kSmemStack][blockDim] refs
-    int nthreads;
-    float lt[kLocalStack];
-    int lr[kLocalStack];
+// The traversal is written as a per-ray state (RayTrav) plus three steps -- trav_inner (one wide node), trav_leaf (one
+// leaf) and trav_pop -- so that the same code serves two schedulers: trace_closest below (one ray to completion: the
+// primary-ray entry point, the wavefront extend kernel, the CPU emulation of the tests) and the megakernel, which
+// interleaves the steps of 32 rays so that a warp executes ONE kind of step at a time (kernels.cu).
+//
+// RayTrav::ref says what the ray does next: >= 0 and < kRefIdle: visit that inner node; < 0: test that leaf;
+// kRefDone: traversal finished (closest hit in htype/hslot/horig/closest).  kRefNeed / kRefIdle are the megakernel's
+// "lane wants a new path" / "no work left" states.
+constexpr int kRefDone = 0x7fffffff;
+constexpr int kRefNeed = 0x7ffffffe;
+constexpr int kRefIdle = 0x7ffffffd;
+__device__ __forceinline__ bool ref_is_leaf(int r) { return r < 0; }
+__device__ __forceinline__ bool ref_is_inner(int r) { return (unsigned int)r < (unsigned int)kRefIdle; }
+
+struct RayTrav {
+    V3 o, d;
+    float idx, idy, idz, oox, ooy, ooz;  // reciprocal direction, origin * reciprocal direction
+    float a, inv_a;                      // |d|^2 and (fast mode) its reciprocal: per-ray constants of the sphere test
+    float tmin, closest, eps;
+    int ref, sp;
+    int htype, hslot, horig;             // closest hit so far: -1 miss / 0 sphere / 1 plane, re-ordered slot, caller's index
+    unsigned int best_key;
 };
 
-template <bool X, bool COUNT>
-__device__ __forceinline__ void trace_closest(const DevScene& sc, const float4* __restrict__ s_top, float* __restrict__ s_st,
-                                              int* __restrict__ s_sr, V3 o, V3 d, float tmin, float tmax, HitInfo& hit,
-                                              WorkCount& wc) {
-    // per-ray constants
+// per-thread stack: kSmemStack entries in shared memory (strided by the block size), the rest in local memory
+struct TravStack {
+    float* st;
+    int* sr;
+    float* lt;
+    int* lr;
+    int tid, nt;
+    __device__ __forceinline__ void push(int sp, float t, int r) const {
+        if (sp < kSmemStack) { st[sp * nt + tid] = t; sr[sp * nt + tid] = r; }
+        else { lt[sp - kSmemStack] = t; lr[sp - kSmemStack] = r; }
+    }
+    __device__ __forceinline__ void load(int sp, float& t, int& r) const {
+        if (sp < kSmemStack) { t = st[sp * nt + tid]; r = sr[sp * nt + tid]; }
+        else { t = lt[sp - kSmemStack]; r = lr[sp - kSmemStack]; }
+    }
+};
+
+template <bool X>
+__device__ __forceinline__ void trav_begin(RayTrav& r, V3 o, V3 d, float tmin, float tmax) {
     const float eps = 1e-20f;
     float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
     float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
     float dz = fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z;
-    const float idx = 1.0f / dx, idy = 1.0f / dy, idz = 1.0f / dz;
-    const float oox = o.x * idx, ooy = o.y * idy, ooz = o.z * idz;
-    const float a = len2_3<X>(d);
-    const float inv_a = X ? 0.0f : 1.0f / a;
+    r.o = o;
+    r.d = d;
+    r.idx = 1.0f / dx; r.idy = 1.0f / dy; r.idz = 1.0f / dz;
+    r.oox = o.x * r.idx; r.ooy = o.y * r.idy; r.ooz = o.z * r.idz;
+    r.a = len2_3<X>(d);
+    r.inv_a = X ? 0.0f : 1.0f / r.a;
+    r.tmin = tmin;
+    r.closest = tmax;
+    // conservative slab test: the far side is widened by a few ulps of the slab products (boxes are padded too)
+    r.eps = 1e-7f * (fabsf(r.oox) + fabsf(r.ooy) + fabsf(r.ooz));
+    r.ref = 0;  // root
+    r.sp = 0;
+    r.htype = -1;
+    r.hslot = -1;
+    r.horig = -1;
+    r.best_key = 0;
+}
 
-    float closest = tmax;
-    hit.type = -1;
-    hit.slot = -1;
-    hit.orig = -1;
-    hit.t = tmax;
-    unsigned int best_key = 0;
+// pops entries until one starts no further than the closest hit; kRefDone when the stack runs out
+__device__ __forceinline__ void trav_pop(RayTrav& r, const TravStack& stk) {
+    r.ref = kRefDone;
+    while (r.sp > 0) {
+        --r.sp;
+        float t;
+        int e;
+        stk.load(r.sp, t, e);
+        if (t <= r.closest) { r.ref = e; break; }
+    }
+}
 
+// one inner node: 7 x 128-bit loads, 4 slab tests, near-first ordering.  Returns true when no child was hit (the
+// caller pops); otherwise r.ref is the nearest child and the others are on the stack, far to near.
+template <bool X, bool COUNT>
+__device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __restrict__ s_top, const TravStack& stk, RayTrav& r,
+                                           WorkCount& wc) {
+    const int ref = r.ref;
+    float4 q0, q1, q2, q3, q4, q5, c;
+    if (ref < sc.top_nodes) {
+        const float4* p = s_top + ref * kTopStride;
+        q0 = p[0]; q1 = p[1]; q2 = p[2]; q3 = p[3]; q4 = p[4]; q5 = p[5];
+        c = p[6];
+    } else {
+        const float4* p = sc.nodes + (size_t)ref * 8;
+        q0 = __ldg(p); q1 = __ldg(p + 1); q2 = __ldg(p + 2); q3 = __ldg(p + 3); q4 = __ldg(p + 4); q5 = __ldg(p + 5);
+        c = __ldg(p + 6);
+    }
+    if (COUNT) wc.nodes++;
+    float tn[4];
+    int cr[4] = {__float_as_int(c.x), __float_as_int(c.y), __float_as_int(c.z), __float_as_int(c.w)};
+    const float lox[4] = {q0.x, q0.y, q0.z, q0.w}, loy[4] = {q1.x, q1.y, q1.z, q1.w}, loz[4] = {q2.x, q2.y, q2.z, q2.w};
+    const float hix[4] = {q3.x, q3.y, q3.z, q3.w}, hiy[4] = {q4.x, q4.y, q4.z, q4.w}, hiz[4] = {q5.x, q5.y, q5.z, q5.w};
+    const float inf = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float x0 = fmaf(lox[i], r.idx, -r.oox), x1 = fmaf(hix[i], r.idx, -r.oox);
+        float y0 = fmaf(loy[i], r.idy, -r.ooy), y1 = fmaf(hiy[i], r.idy, -r.ooy);
+        float z0 = fmaf(loz[i], r.idz, -r.ooz), z1 = fmaf(hiz[i], r.idz, -r.ooz);
+        float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
+        float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), r.closest));
+        bool h = (cr[i] != kEmptyChildDev) && (tnear <= fmaf(tfar, 1.0000005f, r.eps));
+        tn[i] = h ? tnear : inf;
+    }
+    // sorting network on 4 (t, ref) pairs: (0,1)(2,3)(0,2)(1,3)(1,2)
+#define RTB_CSWAP(i, j)                                            \
+    {                                                              \
+        bool s_ = tn[j] < tn[i];                                   \
+        float ta_ = s_ ? tn[j] : tn[i], tb_ = s_ ? tn[i] : tn[j];  \
+        int ra_ = s_ ? cr[j] : cr[i], rb_ = s_ ? cr[i] : cr[j];    \
+        tn[i] = ta_; tn[j] = tb_; cr[i] = ra_; cr[j] = rb_;        \
+    }
+    RTB_CSWAP(0, 1) RTB_CSWAP(2, 3) RTB_CSWAP(0, 2) RTB_CSWAP(1, 3) RTB_CSWAP(1, 2)
+#undef RTB_CSWAP
+    // push far-to-near: entries 3,2,1 ; continue with entry 0
+#pragma unroll
+    for (int i = 3; i >= 1; --i) {
+        if (tn[i] < inf) {
+            stk.push(r.sp, tn[i], cr[i]);
+            ++r.sp;
+        }
+    }
+    if (tn[0] < inf) {
+        r.ref = cr[0];
+        return false;
+    }
+    return true;
+}
+
+// one leaf: up to 4 same-type primitives; the caller pops afterwards
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc) {
+    unsigned int bits = (unsigned int)r.ref;
+    int type = (bits >> 30) & 1, cnt = ((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
+    for (int k = 0; k < cnt; ++k) {
+        float t, al, be;
+        bool h;
+        if (type == 0) {
+            if (COUNT) wc.spheres++;
+            h = sphere_t<X>(r.o, r.d, r.a, r.inv_a, __ldg(sc.spheres + first + k), r.tmin, r.closest, t);
+        } else {
+            if (COUNT) wc.planes++;
+            h = plane_t<X>(r.o, r.d, sc.planes + 5 * (size_t)(first + k), r.tmin, r.closest, t, al, be);
+        }
+        if (h) {
+            int orig = type == 0 ? __ldg(sc.sphere_meta + first + k).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)(first + k) + 3).w);
+            unsigned int key = ((unsigned int)type << 30) | (unsigned int)orig;
+            if (t < r.closest || r.htype < 0 || key > r.best_key) {
+                r.closest = t;
+                r.best_key = key;
+                r.htype = type;
+                r.hslot = first + k;
+                r.horig = orig;
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ HitInfo trav_hit(const RayTrav& r) {
+    HitInfo h;
+    h.t = r.closest;
+    h.type = r.htype;
+    h.slot = r.hslot;
+    h.orig = r.horig;
+    return h;
+}
+
+// one ray to completion
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trace_closest(const DevScene& sc, const float4* __restrict__ s_top, float* __restrict__ s_st,
+                                              int* __restrict__ s_sr, V3 o, V3 d, float tmin, float tmax, HitInfo& hit,
+                                              WorkCount& wc) {
     float lst[kLocalStack];
     int lsr[kLocalStack];
-    const int tid = threadIdx.x, nt = blockDim.x;
-    int sp = 0;
-    int ref = 0;  // root
-
-    for (;;) {
-        bool have = true;
-        if (ref >= 0) {
-            // ---- inner node: 8 x 128-bit loads, 4 slab tests, near-first ordering
-            float4 q0, q1, q2, q3, q4, q5;
-            int4 ch;
-            if (ref < sc.top_nodes) {
-                const float4* p = s_top + ref * kTopStride;
-                q0 = p[0]; q1 = p[1]; q2 = p[2]; q3 = p[3]; q4 = p[4]; q5 = p[5];
-                float4 c = p[6];
-                ch = make_int4(__float_as_int(c.x), __float_as_int(c.y), __float_as_int(c.z), __float_as_int(c.w));
-            } else {
-                const float4* p = sc.nodes + (size_t)ref * 8;
-                q0 = __ldg(p); q1 = __ldg(p + 1); q2 = __ldg(p + 2); q3 = __ldg(p + 3); q4 = __ldg(p + 4); q5 = __ldg(p + 5);
-                float4 c = __ldg(p + 6);
-                ch = make_int4(__float_as_int(c.x), __float_as_int(c.y), __float_as_int(c.z), __float_as_int(c.w));
-            }
-            if (COUNT) wc.nodes++;
-            float tn[4];
-            int cr[4] = {ch.x, ch.y, ch.z, ch.w};
-            const float lox[4] = {q0.x, q0.y, q0.z, q0.w}, loy[4] = {q1.x, q1.y, q1.z, q1.w}, loz[4] = {q2.x, q2.y, q2.z, q2.w};
-            const float hix[4] = {q3.x, q3.y, q3.z, q3.w}, hiy[4] = {q4.x, q4.y, q4.z, q4.w}, hiz[4] = {q5.x, q5.y, q5.z, q5.w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                float x0 = fmaf(lox[i], idx, -oox), x1 = fmaf(hix[i], idx, -oox);
-                float y0 = fmaf(loy[i], idy, -ooy), y1 = fmaf(hiy[i], idy, -ooy);
-                float z0 = fmaf(loz[i], idz, -ooz), z1 = fmaf(hiz[i], idz, -ooz);
-                float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-                float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), closest));
-                // conservative: widen the far side by a few ulps of the slab products (boxes are padded too)
-                bool h = (cr[i] != kEmptyChildDev) && (tnear <= tfar * 1.0000005f + 1e-7f * (fabsf(oox) + fabsf(ooy) + fabsf(ooz)));
-                tn[i] = h ? tnear : __int_as_float(0x7f800000);
-            }
-            // sorting network on 4 (t, ref) pairs: (0,1)(2,3)(0,2)(1,3)(1,2)
-#define RTB_CSWAP(i, j)                                   \
-    {                                                     \
-        bool s_ = tn[j] < tn[i];                          \
-        float ta_ = s_ ? tn[j] : tn[i], tb_ = s_ ? tn[i] : tn[j]; \
-        int ra_ = s_ ? cr[j] : cr[i], rb_ = s_ ? cr[i] : cr[j];   \
-        tn[i] = ta_; tn[j] = tb_; cr[i] = ra_; cr[j] = rb_;       \
+    TravStack stk;
+    stk.st = s_st; stk.sr = s_sr; stk.lt = lst; stk.lr = lsr;
+    stk.tid = threadIdx.x; stk.nt = blockDim.x;
+    RayTrav r;
+    trav_begin<X>(r, o, d, tmin, tmax);
+    while (r.ref != kRefDone) {
+        bool pop = true;
+        if (ref_is_leaf(r.ref)) trav_leaf<X, COUNT>(sc, r, wc);
+        else pop = trav_inner<X, COUNT>(sc, s_top, stk, r, wc);
+        if (pop) trav_pop(r, stk);
     }
-            RTB_CSWAP(0, 1) RTB_CSWAP(2, 3) RTB_CSWAP(0, 2) RTB_CSWAP(1, 3) RTB_CSWAP(1, 2)
-#undef RTB_CSWAP
-            const float inf = __int_as_float(0x7f800000);
-            // push far-to-near: entries 3,2,1 ; continue with entry 0
-#pragma unroll
-            for (int i = 3; i >= 1; --i) {
-                if (tn[i] < inf) {
-                    if (sp < kSmemStack) { s_st[sp * nt + tid] = tn[i]; s_sr[sp * nt + tid] = cr[i]; }
-                    else { lst[sp - kSmemStack] = tn[i]; lsr[sp - kSmemStack] = cr[i]; }
-                    ++sp;
-                }
-            }
-            if (tn[0] < inf) { ref = cr[0]; continue; }
-            have = false;
-        } else {
-            // ---- leaf: up to 4 same-type primitives
-            unsigned int bits = (unsigned int)ref;
-            int type = (bits >> 30) & 1, cnt = ((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
-            for (int k = 0; k < cnt; ++k) {
-                float t, al, be;
-                bool h;
-                if (type == 0) {
-                    if (COUNT) wc.spheres++;
-                    h = sphere_t<X>(o, d, a, inv_a, __ldg(sc.spheres + first + k), tmin, closest, t);
-                } else {
-                    if (COUNT) wc.planes++;
-                    h = plane_t<X>(o, d, sc.planes + 5 * (size_t)(first + k), tmin, closest, t, al, be);
-                }
-                if (h) {
-                    int orig = type == 0 ? __ldg(sc.sphere_meta + first + k).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)(first + k) + 3).w);
-                    unsigned int key = ((unsigned int)type << 30) | (unsigned int)orig;
-                    if (t < closest || hit.type < 0 || key > best_key) {
-                        closest = t;
-                        best_key = key;
-                        hit.t = t;
-                        hit.type = type;
-                        hit.slot = first + k;
-                        hit.orig = orig;
-                    }
-                }
-            }
-            have = false;
-        }
-        // ---- pop (skip entries that start beyond the current closest hit)
-        while (!have && sp > 0) {
-            --sp;
-            float t;
-            int r;
-            if (sp < kSmemStack) { t = s_st[sp * nt + tid]; r = s_sr[sp * nt + tid]; }
-            else { t = lst[sp - kSmemStack]; r = lsr[sp - kSmemStack]; }
-            if (t <= closest) { ref = r; have = true; }
-        }
-        if (!have) break;
-    }
+    hit = trav_hit(r);
 }
 
 }  // namespace rtb
