@@ -34,7 +34,7 @@ enum {
     RT_ERR_UNSUPPORTED = 4
 };
 
-enum { RT_KERNEL_MEGA = 0, RT_KERNEL_WAVEFRONT = 1 };
+enum { RT_KERNEL_MEGA = 0, RT_KERNEL_WAVEFRONT = 1, RT_KERNEL_POOL = 2 };
 enum { RT_RNG_PHILOX = 0,      /* counter-based Philox4x32-10 keyed on (seed; pixel, sample, bounce) -- production */
        RT_RNG_REFERENCE = 1 }; /* the reference's stateful wang_hash stream (include/random_utils.h) incl. its
                                   rejection loops -- parity mode: reproduces the reference host render per sample */

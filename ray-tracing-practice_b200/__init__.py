@@ -14,7 +14,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "librt_b200.so")
+LIB_PATH = os.environ.get("RTB_LIB") or os.path.join(HERE, "librt_b200.so")  # RTB_LIB: a tuning build (make variant)
 
 # numpy images of the reference PODs that cross the boundary (include/rt_b200.h)
 SPHERE = np.dtype({"names": ["center", "radius", "material_idx"], "formats": [("<f4", 3), "<f4", "<i4"],
@@ -32,7 +32,7 @@ CAMERA = np.dtype({"names": ["origin", "pixel00_loc", "pixel_delta_u", "pixel_de
 
 LAMBERTIAN, METAL, DIELECTRIC, DIFFUSE_LIGHT = 0, 1, 2, 3
 QUAD, ELLIPSE, TRIANGLE = 0, 1, 2
-KERNEL_MEGA, KERNEL_WAVEFRONT = 0, 1
+KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_POOL = 0, 1, 2
 RNG_PHILOX, RNG_REFERENCE = 0, 1
 TEX_CPU, TEX_GPU = 0, 1
 TILE = 16

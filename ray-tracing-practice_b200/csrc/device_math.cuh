@@ -101,7 +101,11 @@ template <> struct Rng<kRngReference> {
     uint32_t s;
     // per-sample seeding exactly as render_kernel / render_cpu: src/camera.cu:25-28 (note x*W + y)
     __device__ __forceinline__ void begin_sample(uint32_t pixel_base, uint32_t sample, uint32_t, uint2) { s = wang_hash_u32(pixel_base + sample); }
+    __device__ __forceinline__ void attach(uint32_t, uint32_t, uint2) {}
     __device__ __forceinline__ void begin_bounce(uint32_t) {}
+    // the stream's whole state is one word: what a path parks between segments
+    __device__ __forceinline__ uint32_t save() const { return s; }
+    __device__ __forceinline__ void restore(uint32_t w) { s = w; }
     __device__ __forceinline__ float next() {
         s = wang_hash_u32(s);
         return __fdiv_rn((float)s, 4294967296.0f);
@@ -109,27 +113,36 @@ template <> struct Rng<kRngReference> {
 };
 
 template <> struct Rng<kRngPhilox> {
-    uint4 c;   // counter
-    uint4 v;   // current block
+    // ONE Philox block = the four uniforms of one path vertex: the camera jitter of a sample (bounce 0) or one scatter
+    // event (bounce b >= 1 needs at most 4: lobe choice + 3 for the fuzz ball).  The block is generated eagerly at
+    // begin_sample / begin_bounce -- a single call site that every lane of a shading pass reaches together -- and
+    // next() only hands out its words, so no Philox code is replicated into the divergent material branches.
+    uint4 c;   // counter (pixel, sample, bounce, 0)
+    uint4 v;   // the block
     uint2 key;
     int used;
-    __device__ __forceinline__ void begin_sample(uint32_t, uint32_t sample, uint32_t pixel, uint2 k) {
+    // binds the stream to (pixel, sample) without generating anything (what a path does when it resumes)
+    __device__ __forceinline__ void attach(uint32_t sample, uint32_t pixel, uint2 k) {
         key = k;
         c = make_uint4(pixel, sample, 0u, 0u);
         used = 4;
     }
+    __device__ __forceinline__ void begin_sample(uint32_t, uint32_t sample, uint32_t pixel, uint2 k) {
+        attach(sample, pixel, k);
+        v = philox4x32_10(c, key);
+        used = 0;
+    }
+    // counter-based: nothing to park, the counter is rebuilt from (pixel, sample, bounce)
+    __device__ __forceinline__ uint32_t save() const { return 0u; }
+    __device__ __forceinline__ void restore(uint32_t) {}
     __device__ __forceinline__ void begin_bounce(uint32_t bounce) {
         c.z = bounce;
         c.w = 0u;
-        used = 4;
+        v = philox4x32_10(c, key);
+        used = 0;
     }
     __device__ __forceinline__ float next() {
-        if (used == 4) {
-            v = philox4x32_10(c, key);
-            c.w++;
-            used = 0;
-        }
-        uint32_t r = used == 0 ? v.x : used == 1 ? v.y : used == 2 ? v.z : v.w;
+        uint32_t r = used == 0 ? v.x : used == 1 ? v.y : used == 2 ? v.z : v.w;  // `used` folds to a constant per path
         used++;
         return (float)(r >> 8) * (1.0f / 16777216.0f);  // [0,1)
     }

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     const int shade_min = fp.shade_min, leaf_min = fp.leaf_min;
 
     // warp-uniform tile pool
-    int pool_tile = 0, pool_next = kTile * kTile;
+    int pool_tile = 0, pool_blk = 0, pool_next = kBlockPixels;
     bool exhausted = false;
 
     // per-lane state
@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     ps.o = mk3(0, 0, 0); ps.d = mk3(0, 0, 1); ps.beta = mk3(1, 1, 1); ps.L = mk3(0, 0, 0); ps.depth = 0;
     V3 acc = mk3(0, 0, 0);
     Rng<MODE> rng;
-    rng.begin_sample(0u, 0u, 0u, fp.key);
+    rng.attach(0u, 0u, fp.key);
     uint32_t pixel_base = 0;
     WorkCount wc = {0, 0, 0, 0, 0, 0};
 
@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             // ---- SHADE 1: second half of the finished segments (miss -> background, else emission + scatter)
             bool start_ray = false;
             if (rt.ref == kRefDone) {
-                if (MODE == kRngPhilox) rng.begin_sample(pixel_base, (uint32_t)sample, (uint32_t)(py * W + px), fp.key);
+                rng.attach((uint32_t)sample, (uint32_t)(py * W + px), fp.key);
                 if (finish_segment<MODE, X, COUNT>(sc, fp.cam, fp.tex_mode, trav_hit(rt), ps, rng, wc)) {
                     // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
                     acc = add3<X>(acc, ps.L);
@@ -84,21 +84,22 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             // ---- SHADE 2: hand out pixels to lanes that have none (warp-aggregated fetch)
             unsigned need = __ballot_sync(full, rt.ref == kRefNeed && !has_pixel);
             while (need && !exhausted) {
-                if (pool_next >= kTile * kTile) {
+                if (pool_next >= kBlockPixels) {
                     unsigned k = 0;
                     if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
                     k = __shfl_sync(full, k, 0);
-                    if ((int)k >= fp.my_tiles) { exhausted = true; break; }
-                    pool_tile = (int)k * fp.tile_nranks + fp.tile_rank;
+                    if ((int)(k / kBlocksPerTile) >= fp.my_tiles) { exhausted = true; break; }
+                    pool_tile = (int)(k / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
+                    pool_blk = (int)(k % kBlocksPerTile);
                     pool_next = 0;
                 }
-                int avail = kTile * kTile - pool_next;
+                int avail = kBlockPixels - pool_next;
                 int rank = __popc(need & ((1u << lane) - 1u));
                 if (rt.ref == kRefNeed && !has_pixel && rank < avail) {
                     int q = pool_next + rank;
-                    int blk = q >> 5;  // 8 blocks of 8x4 pixels inside the 16x16 tile
+                    int blk = pool_blk;  // 8 blocks of 8x4 pixels inside the 16x16 tile
                     int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
-                    int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
+                    int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + (q >> 3);
                     if (x < W && y < H && (spp <= 0 || fp.cam.depth <= 0)) {
                         float* out = fp.fb + 3 * ((size_t)y * W + x);  // no samples / no segments: the pixel is black
                         out[0] = 0.f; out[1] = 0.f; out[2] = 0.f;

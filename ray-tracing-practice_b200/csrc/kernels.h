@@ -26,14 +26,28 @@ struct LaunchCfg {
 };
 
 constexpr int kTile = 16;  // == RT_TILE
-constexpr int kMegaThreads = 256;
-constexpr int kMegaBlocksPerSM = 2;
-constexpr int kShadeMinDefault = 24;
-constexpr int kLeafMinDefault = 8;
+// the unit of work a warp fetches with one atomicAdd: an 8x4-pixel block (one pixel per lane) of a 16x16 tile.  Tiles
+// stay the unit of the multi-GPU partition; blocks keep the end-of-frame tail short (8x more, 8x smaller work items).
+constexpr int kBlockPixels = 32;
+constexpr int kBlocksPerTile = kTile * kTile / kBlockPixels;
+#ifndef RTB_MEGA_THREADS
+#define RTB_MEGA_THREADS 256
+#endif
+#ifndef RTB_MEGA_BLOCKS
+#define RTB_MEGA_BLOCKS 2
+#endif
+constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of the persistent kernels
+constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM they are compiled (register-capped) for
+constexpr int kShadeMinDefault = 32;
+constexpr int kLeafMinDefault = 16;
 
 // persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1
 cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
                                cudaStream_t stream);
+// persistent megakernel with a per-warp path pool in shared memory (mega_pool.cu)
+cudaError_t launch_render_pool(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
+                               cudaStream_t stream);
+size_t pool_smem_bytes(int top_nodes, int threads);
 // wavefront variant (generate / extend / shade kernels over global queues); scratch is owned by the caller
 struct WavefrontScratch {
     void* buf = nullptr;

@@ -258,7 +258,7 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     memcpy(&fp.cam, cam76, sizeof(CameraPod));
     if (fp.cam.W <= 0 || fp.cam.H <= 0 || fp.cam.spp < 0 || fp.cam.depth < 0) return fail(RT_ERR_INVALID, "rt_render: bad CameraData");
     if (o.tile_rank < 0 || o.tile_rank >= o.tile_nranks) return fail(RT_ERR_INVALID, "rt_render: tile_rank out of range");
-    if (o.kernel != RT_KERNEL_MEGA && o.kernel != RT_KERNEL_WAVEFRONT) return fail(RT_ERR_INVALID, "rt_render: unknown kernel");
+    if (o.kernel != RT_KERNEL_MEGA && o.kernel != RT_KERNEL_WAVEFRONT && o.kernel != RT_KERNEL_POOL) return fail(RT_ERR_INVALID, "rt_render: unknown kernel");
     fp.key = make_uint2((unsigned)(o.seed & 0xffffffffu), (unsigned)(o.seed >> 32));
     fp.tex_mode = o.tex_mode;
     fp.tile_rank = o.tile_rank;
@@ -287,6 +287,7 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
     RT_CUDA(cudaEventRecord(s->ev0, stream));
     if (o.kernel == RT_KERNEL_MEGA) RT_CUDA(launch_render_mega(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
+    else if (o.kernel == RT_KERNEL_POOL) RT_CUDA(launch_render_pool(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else RT_CUDA(launch_render_wavefront(dev, fp, o.rng, o.exact_math, o.count_work, cfg, s->wf, stream));
     RT_CUDA(cudaEventRecord(s->ev1, stream));
     s->pending = true;

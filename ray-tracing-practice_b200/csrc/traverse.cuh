@@ -29,8 +29,11 @@ struct DevScene {
     int top_nodes;                           // wide nodes [0, top_nodes) are staged in shared memory
 };
 
-constexpr int kSmemStack = 12;   // per-thread stack entries held in shared memory
-constexpr int kLocalStack = 52;  // overflow entries (local memory); builder guarantees max_stack <= 64
+#ifndef RTB_SMEM_STACK
+#define RTB_SMEM_STACK 12
+#endif
+constexpr int kSmemStack = RTB_SMEM_STACK;       // per-thread stack entries held in shared memory
+constexpr int kLocalStack = 64 - kSmemStack;     // overflow entries (local memory); builder guarantees max_stack <= 64
 constexpr int kTopStride = 9;    // float4 per staged node: 8 + 1 pad (144 B) so 128-bit LDS spread over banks
 constexpr int32_t kEmptyChildDev = 0x7fffffff;
 
@@ -131,6 +134,7 @@ struct RayTrav {
     float idx, idy, idz, oox, ooy, ooz;  // reciprocal direction, origin * reciprocal direction
     float a, inv_a;                      // |d|^2 and (fast mode) its reciprocal: per-ray constants of the sphere test
     float tmin, closest, eps;
+    int nx, ny, nz;                      // which float4 of the node holds the NEAR slab plane per axis (lo for d >= 0, hi for d < 0)
     int ref, sp;
     int htype, hslot, horig;             // closest hit so far: -1 miss / 0 sphere / 1 plane, re-ordered slot, caller's index
     unsigned int best_key;
@@ -169,6 +173,9 @@ __device__ __forceinline__ void trav_begin(RayTrav& r, V3 o, V3 d, float tmin, f
     r.closest = tmax;
     // conservative slab test: the far side is widened by a few ulps of the slab products (boxes are padded too)
     r.eps = 1e-7f * (fabsf(r.oox) + fabsf(r.ooy) + fabsf(r.ooz));
+    r.nx = dx < 0.0f ? 3 : 0;
+    r.ny = dy < 0.0f ? 4 : 1;
+    r.nz = dz < 0.0f ? 5 : 2;
     r.ref = 0;  // root
     r.sp = 0;
     r.htype = -1;
@@ -191,34 +198,37 @@ __device__ __forceinline__ void trav_pop(RayTrav& r, const TravStack& stk) {
 
 // one inner node: 7 x 128-bit loads, 4 slab tests, near-first ordering.  Returns true when no child was hit (the
 // caller pops); otherwise r.ref is the nearest child and the others are on the stack, far to near.
+// The near / far plane of each axis is chosen by the LOAD ADDRESS (per-ray constants nx, ny, nz), not by min/max of
+// both products; empty slots hold lo = +inf, hi = -inf and fail the test on their own.
 template <bool X, bool COUNT>
 __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __restrict__ s_top, const TravStack& stk, RayTrav& r,
                                            WorkCount& wc) {
     const int ref = r.ref;
-    float4 q0, q1, q2, q3, q4, q5, c;
+    float4 nx4, ny4, nz4, fx4, fy4, fz4, c;
     if (ref < sc.top_nodes) {
         const float4* p = s_top + ref * kTopStride;
-        q0 = p[0]; q1 = p[1]; q2 = p[2]; q3 = p[3]; q4 = p[4]; q5 = p[5];
+        nx4 = p[r.nx]; ny4 = p[r.ny]; nz4 = p[r.nz]; fx4 = p[3 - r.nx]; fy4 = p[5 - r.ny]; fz4 = p[7 - r.nz];
         c = p[6];
     } else {
         const float4* p = sc.nodes + (size_t)ref * 8;
-        q0 = __ldg(p); q1 = __ldg(p + 1); q2 = __ldg(p + 2); q3 = __ldg(p + 3); q4 = __ldg(p + 4); q5 = __ldg(p + 5);
+        nx4 = __ldg(p + r.nx); ny4 = __ldg(p + r.ny); nz4 = __ldg(p + r.nz);
+        fx4 = __ldg(p + (3 - r.nx)); fy4 = __ldg(p + (5 - r.ny)); fz4 = __ldg(p + (7 - r.nz));
         c = __ldg(p + 6);
     }
     if (COUNT) wc.nodes++;
     float tn[4];
     int cr[4] = {__float_as_int(c.x), __float_as_int(c.y), __float_as_int(c.z), __float_as_int(c.w)};
-    const float lox[4] = {q0.x, q0.y, q0.z, q0.w}, loy[4] = {q1.x, q1.y, q1.z, q1.w}, loz[4] = {q2.x, q2.y, q2.z, q2.w};
-    const float hix[4] = {q3.x, q3.y, q3.z, q3.w}, hiy[4] = {q4.x, q4.y, q4.z, q4.w}, hiz[4] = {q5.x, q5.y, q5.z, q5.w};
+    const float nxs[4] = {nx4.x, nx4.y, nx4.z, nx4.w}, nys[4] = {ny4.x, ny4.y, ny4.z, ny4.w}, nzs[4] = {nz4.x, nz4.y, nz4.z, nz4.w};
+    const float fxs[4] = {fx4.x, fx4.y, fx4.z, fx4.w}, fys[4] = {fy4.x, fy4.y, fy4.z, fy4.w}, fzs[4] = {fz4.x, fz4.y, fz4.z, fz4.w};
     const float inf = __int_as_float(0x7f800000);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        float x0 = fmaf(lox[i], r.idx, -r.oox), x1 = fmaf(hix[i], r.idx, -r.oox);
-        float y0 = fmaf(loy[i], r.idy, -r.ooy), y1 = fmaf(hiy[i], r.idy, -r.ooy);
-        float z0 = fmaf(loz[i], r.idz, -r.ooz), z1 = fmaf(hiz[i], r.idz, -r.ooz);
-        float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
-        float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), r.closest));
-        bool h = (cr[i] != kEmptyChildDev) && (tnear <= fmaf(tfar, 1.0000005f, r.eps));
+        float x0 = fmaf(nxs[i], r.idx, -r.oox), x1 = fmaf(fxs[i], r.idx, -r.oox);
+        float y0 = fmaf(nys[i], r.idy, -r.ooy), y1 = fmaf(fys[i], r.idy, -r.ooy);
+        float z0 = fmaf(nzs[i], r.idz, -r.ooz), z1 = fmaf(fzs[i], r.idz, -r.ooz);
+        float tnear = fmaxf(fmaxf(x0, y0), fmaxf(z0, r.tmin));
+        float tfar = fminf(fminf(x1, y1), fminf(z1, r.closest));
+        bool h = tnear <= fmaf(tfar, 1.0000005f, r.eps);
         tn[i] = h ? tnear : inf;
     }
     // sorting network on 4 (t, ref) pairs: (0,1)(2,3)(0,2)(1,3)(1,2)

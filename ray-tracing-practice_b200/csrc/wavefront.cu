@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(256) wf_shade(const __grid_constant__ DevScene
             } else {
                 int slot = id % st.slots, k = id / st.slots, x, y;
                 slot_pixel(fp, slot, x, y);
-                rng.begin_sample(0u, (uint32_t)(s0 + k), (uint32_t)(y * fp.cam.W + x), fp.key);
+                rng.attach((uint32_t)(s0 + k), (uint32_t)(y * fp.cam.W + x), fp.key);
             }
             alive = !finish_segment<MODE, X, COUNT>(sc, fp.cam, fp.tex_mode, hit, ps, rng, wc);
             st.L[0][id] = ps.L.x; st.L[1][id] = ps.L.y; st.L[2][id] = ps.L.z;

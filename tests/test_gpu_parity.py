@@ -140,6 +140,19 @@ def test_kernel_variants_agree(rt, test_scene):
     p, ip = sc.render(g["camera"], seed=3)
     q, iq = sc.render(g["camera"], seed=3, kernel=rt.KERNEL_WAVEFRONT)
     assert p.tobytes() == q.tobytes() and ip["segments"] == iq["segments"]
+    # the pooled megakernel: same streams, same per-pixel summation order => same bits, also at odd sizes / tile splits
+    c, ic = sc.render(g["camera"], rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU, kernel=rt.KERNEL_POOL, count_work=True)
+    assert a.tobytes() == c.tobytes() and ia["segments"] == ic["segments"] and ic["samples"] == 200 * 100 * 4
+    w, iw = sc.render(g["camera"], seed=3, kernel=rt.KERNEL_POOL)
+    assert p.tobytes() == w.tobytes() and ip["segments"] == iw["segments"]
+    cam = g["camera"].copy()
+    cam["samples_per_pixel"] = 0
+    z, iz = sc.render(cam, kernel=rt.KERNEL_POOL)
+    assert (z == 0).all() and iz["segments"] == 0
+    for rank in range(3):
+        t0, _ = sc.render(g["camera"], seed=3, tile_rank=rank, tile_nranks=3)
+        t1, _ = sc.render(g["camera"], seed=3, tile_rank=rank, tile_nranks=3, kernel=rt.KERNEL_POOL)
+        assert t0.tobytes() == t1.tobytes()
     for top in (0, 1, 16, 64):
         r, _ = sc.render(g["camera"], seed=3, top_nodes=top)
         assert r.tobytes() == p.tobytes()  # staging the top levels in shared memory changes nothing but speed

@@ -17,7 +17,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
     ap.add_argument("--depth", type=int, default=0)
     ap.add_argument("--reps", type=int, default=3)
-    ap.add_argument("--kernel", default="mega", choices=["mega", "wavefront"])
+    ap.add_argument("--kernel", default="mega", choices=["mega", "wavefront", "pool"])
     ap.add_argument("--rng", default="philox", choices=["philox", "reference"])
     ap.add_argument("--exact", action="store_true")
     ap.add_argument("--count", action="store_true")
@@ -33,7 +33,7 @@ def main():
     if a.depth:
         cam["max_depth"] = a.depth
     fb = np.zeros((cfg["H"], cfg["W"], 3), np.float32)
-    kw = dict(kernel=rt.KERNEL_MEGA if a.kernel == "mega" else rt.KERNEL_WAVEFRONT,
+    kw = dict(kernel={"mega": rt.KERNEL_MEGA, "wavefront": rt.KERNEL_WAVEFRONT, "pool": rt.KERNEL_POOL}[a.kernel],
               rng=rt.RNG_PHILOX if a.rng == "philox" else rt.RNG_REFERENCE, exact=a.exact, top_nodes=a.top_nodes)
     best = None
     for _ in range(a.reps):
