@@ -3,20 +3,20 @@
 // render_mega replaces the reference's render_kernel + ray_color (src/camera.cu:17-34, 218-252).  The reference
 // maps one thread to one pixel and runs its whole spp x depth loop nest there, so a warp lives as long as its
 // slowest pixel and dead lanes idle through every bounce.  Here the kernel is PERSISTENT (one grid sized to the
-// machine: SMs x resident CTAs) and a warp is a scheduler over 32 independent path states.  Every lane is in one of
-// four states -- inner node pending, leaf pending, hit ready to shade / new path wanted, idle -- and each loop
-// iteration the warp votes (ballot/popc) on which kind of step to execute:
-//   * SHADE when enough lanes have finished their segment (or nothing else can run): emission + scatter of the hit,
-//     the next sample of the lane's pixel when the path ended, the next pixel when the pixel is complete.  Lanes never
-//     wait for the longest path or the longest traversal of their warp; they wait at most until `shade_min` lanes
-//     have gathered, so the divergent shading code always runs with a useful number of lanes;
-//   * LEAF when enough lanes hold a leaf (or no lane holds an inner node): the primitive tests run together instead
-//     of once per lane inside a divergent branch of the node loop;
-//   * INNER for every lane that holds an inner node: the hot, branch-free part, executed by most lanes every iteration.
-//   Pixels come from 16x16 tiles: a warp whose tile is used up fetches the next tile id with ONE atomicAdd (lane 0)
-//   and a shuffle broadcast -- work fetch is warp-aggregated, ballot/popc ranks hand the pixels to the lanes that
-//   need one.  Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and
-//   stored once, so the output is deterministic and, in parity mode, comparable bit for bit.
+// machine: SMs x resident CTAs) and a warp alternates between two phases, all 32 lanes in phase:
+//   SHADE  every lane finishes the segment it just traced (miss -> background; hit -> emission + scatter, one Philox
+//          block drawn at a single site).  A lane whose path ended starts the next sample of ITS pixel in the same
+//          phase, so lanes never idle on path-length variance (62 % of paths end at the first vertex, the tail runs to
+//          max_depth); a lane whose pixel is complete takes the next pixel of the warp's current work item.  Work
+//          items are 8x4-pixel blocks of the 16x16 tiles, fetched with ONE atomicAdd per warp (lane 0) and a shuffle
+//          broadcast; ballot/popc ranks hand the pixels to the lanes that need one.
+//   TRACE  a while-while traversal of the 32 segments: each iteration the warp votes (ballot/popc); lanes holding an
+//          inner node visit it, lanes holding a leaf wait until `leaf_min` of them have gathered (or no inner node is
+//          left) so the primitive tests run together instead of once per lane inside the node loop.
+// Measured alternatives that lost and why are in DESIGN.md: letting lanes leave the phase (shade as soon as k lanes
+// are done) and the pooled variant (mega_pool.cu) raise lane occupancy of the shading code but run 10-45 % slower.
+// Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored once,
+// so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
 #include "path.cuh"
 #include "smem_top.cuh"
@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int W = fp.cam.W, H = fp.cam.H, spp = fp.cam.spp;
-    const int shade_min = fp.shade_min, leaf_min = fp.leaf_min;
+    const int leaf_min = fp.leaf_min;
 
     // warp-uniform tile pool
     int pool_tile = 0, pool_blk = 0, pool_next = kBlockPixels;
@@ -59,10 +59,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     WorkCount wc = {0, 0, 0, 0, 0, 0};
 
     for (;;) {
-        const unsigned smask = __ballot_sync(full, rt.ref == kRefDone || rt.ref == kRefNeed);
-        const unsigned tmask = __ballot_sync(full, ref_is_leaf(rt.ref) || ref_is_inner(rt.ref));
-        if (smask == 0u && tmask == 0u) break;  // every lane idle
-        if (smask != 0u && (__popc(smask) >= shade_min || tmask == 0u)) {
+        // ================= SHADE phase: every lane of the warp is between two segments (in phase)
+        {
             // ---- SHADE 1: second half of the finished segments (miss -> background, else emission + scatter)
             bool start_ray = false;
             if (rt.ref == kRefDone) {
@@ -127,18 +125,23 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             }
             if (start_ray) trav_begin<X>(rt, ps.o, ps.d, 0.001f, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
         }
-        // ---- LEAF: primitive tests, when enough lanes hold a leaf or no lane has an inner node to visit
-        const unsigned lmask = __ballot_sync(full, ref_is_leaf(rt.ref));
-        const unsigned imask = __ballot_sync(full, ref_is_inner(rt.ref));
-        if (lmask != 0u && (__popc(lmask) >= leaf_min || imask == 0u)) {
-            if (ref_is_leaf(rt.ref)) {
-                trav_leaf<X, COUNT>(sc, rt, wc);
-                trav_pop(rt, stk);
+        if (__all_sync(full, rt.ref == kRefIdle)) break;  // no pixels left for any lane
+        // ================= TRACE phase: while-while traversal of the warp's 32 segments.  Inner nodes are visited by
+        // every lane that holds one; lanes that reach a leaf wait until `leaf_min` of them have gathered (or nobody has
+        // an inner node left), so the primitive tests run with many lanes instead of once per lane per iteration.
+        for (;;) {
+            const unsigned lmask = __ballot_sync(full, ref_is_leaf(rt.ref));
+            const unsigned imask = __ballot_sync(full, ref_is_inner(rt.ref));
+            if ((lmask | imask) == 0u) break;
+            if (lmask != 0u && (__popc(lmask) >= leaf_min || imask == 0u)) {
+                if (ref_is_leaf(rt.ref)) {
+                    trav_leaf<X, COUNT>(sc, rt, wc);
+                    trav_pop(rt, stk);
+                }
             }
-        }
-        // ---- INNER: one wide node for every lane that holds one
-        if (ref_is_inner(rt.ref)) {
-            if (trav_inner<X, COUNT>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+            if (ref_is_inner(rt.ref)) {
+                if (trav_inner<X, COUNT>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+            }
         }
     }
 

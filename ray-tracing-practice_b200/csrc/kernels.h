@@ -13,7 +13,8 @@ struct FrameParams {
     int tex_mode;       // 0 cpu semantics, 1 texture unit
     int tile_rank, tile_nranks;
     int tiles_x, tiles_y, my_tiles;
-    int shade_min, leaf_min;          // megakernel scheduling thresholds (lanes), see kernels.cu
+    int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
+    int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
     float* fb;                        // W*H*3 sums
     unsigned int* tile_counter;       // work queue head (zeroed before launch)
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
@@ -38,8 +39,7 @@ constexpr int kBlocksPerTile = kTile * kTile / kBlockPixels;
 #endif
 constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of the persistent kernels
 constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM they are compiled (register-capped) for
-constexpr int kShadeMinDefault = 32;
-constexpr int kLeafMinDefault = 16;
+constexpr int kLeafMinDefault = 12;
 
 // persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1
 cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,

@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
     const unsigned lt_mask = (1u << lane) - 1u;
     WarpPool wp;
     wp.f = reinterpret_cast<float*>(ts.sr + kSmemStack * blockDim.x) + (threadIdx.x >> 5) * kPoolWords;
-    const int refill_min = fp.shade_min, leaf_min = fp.leaf_min;
+    const int refill_min = fp.refill_min, leaf_min = fp.leaf_min, park_min = fp.park_min;
 
     WarpSched ws;
     ws.pool_tile = 0; ws.pool_blk = 0; ws.pool_next = kBlockPixels; ws.exhausted = false;
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
         }
         // ---- SHADE: a full warp of parked hits, or whatever is parked when lanes starve
         const unsigned starve = __ballot_sync(full, rt.ref == kRefIdle);
-        if (ws.hit_cnt >= 32 || (ws.hit_cnt > 0 && ws.ready_cnt == 0 && starve != 0u)) {
+        if (ws.hit_cnt >= park_min || (ws.hit_cnt > 0 && ws.ready_cnt == 0 && starve != 0u)) {
             const int n = min(ws.hit_cnt, 32);
             const int s = wp.in(kFHitQ, (ws.hit_head + lane) & (kPool - 1));
             ws.hit_head = (ws.hit_head + n) & (kPool - 1);

@@ -276,13 +276,16 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     if (top > 1024) top = 1024;
     dev.top_nodes = top;
     LaunchCfg cfg{s->num_sms, kMegaBlocksPerSM, kMegaThreads};
-    // scheduling thresholds of the megakernel; RTB_SHADE_MIN / RTB_LEAF_MIN are tuning knobs for profiling runs
-    fp.shade_min = kShadeMinDefault;
+    // scheduling thresholds of the megakernels; the RTB_* variables are tuning knobs for profiling runs
     fp.leaf_min = kLeafMinDefault;
-    if (const char* e = getenv("RTB_SHADE_MIN")) fp.shade_min = atoi(e);
     if (const char* e = getenv("RTB_LEAF_MIN")) fp.leaf_min = atoi(e);
-    if (fp.shade_min < 1) fp.shade_min = 1;
     if (fp.leaf_min < 1) fp.leaf_min = 1;
+    fp.refill_min = 32;
+    fp.park_min = 32;
+    if (const char* e = getenv("RTB_REFILL_MIN")) fp.refill_min = atoi(e);
+    if (const char* e = getenv("RTB_PARK_MIN")) fp.park_min = atoi(e);
+    if (fp.refill_min < 1) fp.refill_min = 1;
+    if (fp.park_min < 1) fp.park_min = 1;
     RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, 64, stream));
     RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
     RT_CUDA(cudaEventRecord(s->ev0, stream));
