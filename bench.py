@@ -268,8 +268,12 @@ def main():
     fp32_peak = torch.cuda.get_device_properties(dev).multi_processor_count * FP32_LANES_PER_SM * 2 * sm_mhz * 1e6 / 1e12
     kernel_rays_s = segs_all / world / (kms_total * 1e-3) if kms_total > 0 else 0.0  # per GPU, render kernel only
     achieved = kernel_rays_s * fpr / 1e12
+    traffic, traffic_src = None, None
+    tp = os.path.join(ROOT, "profiles", "r01_ncu_mega_headline.json")   # dram__bytes_read+write of one render_mega launch (ncu --set full)
+    if args.workload == DEFAULT_WORKLOAD and args.kernel == "mega" and os.path.exists(tp):
+        traffic, traffic_src = json.load(open(tp))["traffic_bytes_per_launch"], "profiles/r01_ncu_mega_headline.json"
     roofline = {"bound": "fp32_issue", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                "traffic": None, "kernel": "render_mega" if args.kernel == "mega" else "wf_extend",
+                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": bpr * segs_all / world / args.steps, "kernel": "render_mega" if args.kernel == "mega" else "wf_extend",
                 "kernel_ms_per_launch": kms_total / args.steps, "flops_per_ray": fpr, "bytes_per_ray": bpr, "per_ray": per_ray,
                 "peak_source": "148 SMs x 128 fp32 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json (%s); HBM %.0f GB/s (%s) is not the bound: "
                                "the working set is L2 resident" % (peak_src, peaks.get("hbm_gbs", 0), peak_src),
