@@ -51,7 +51,7 @@ class RtError(RuntimeError):
 class RenderOpts(C.Structure):
     _fields_ = [("struct_size", C.c_int), ("kernel", C.c_int), ("rng", C.c_int), ("exact_math", C.c_int),
                 ("tex_mode", C.c_int), ("seed", C.c_ulonglong), ("tile_rank", C.c_int), ("tile_nranks", C.c_int),
-                ("count_work", C.c_int), ("top_nodes_in_smem", C.c_int)]
+                ("count_work", C.c_int), ("top_nodes_in_smem", C.c_int), ("sample_chunk", C.c_int)]
 
 
 class WorkCounters(C.Structure):
@@ -282,11 +282,12 @@ class Scene:
 
     @staticmethod
     def _opts(kernel=KERNEL_MEGA, rng=RNG_PHILOX, exact=False, tex_mode=TEX_GPU, seed=0, tile_rank=0, tile_nranks=1,
-              count_work=False, top_nodes=-1):
+              count_work=False, top_nodes=-1, sample_chunk=0):
         o = RenderOpts()
         o.struct_size = C.sizeof(RenderOpts)
         o.kernel, o.rng, o.exact_math, o.tex_mode, o.seed = kernel, rng, int(exact), tex_mode, seed
         o.tile_rank, o.tile_nranks, o.count_work, o.top_nodes_in_smem = tile_rank, tile_nranks, int(count_work), top_nodes
+        o.sample_chunk = sample_chunk
         return o
 
     def render(self, cam, out=None, **kw):

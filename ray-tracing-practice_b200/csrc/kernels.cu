@@ -38,10 +38,10 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int W = fp.cam.W, H = fp.cam.H, spp = fp.cam.spp;
-    const int leaf_min = fp.leaf_min;
+    const int leaf_min = fp.leaf_min, nchunks = fp.nchunks;
 
     // warp-uniform tile pool
-    int pool_tile = 0, pool_blk = 0, pool_next = kBlockPixels;
+    int pool_tile = 0, pool_blk = 0, pool_s0 = 0, pool_next = kBlockPixels;
     bool exhausted = false;
 
     // per-lane state
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     trav_begin<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
     rt.ref = kRefNeed;
     bool has_pixel = false;
-    int px = 0, py = 0, sample = 0;
+    int px = 0, py = 0, sample = 0, s_end = 0;
     PathState ps;
     ps.o = mk3(0, 0, 0); ps.d = mk3(0, 0, 1); ps.beta = mk3(1, 1, 1); ps.L = mk3(0, 0, 0); ps.depth = 0;
     V3 acc = mk3(0, 0, 0);
@@ -69,8 +69,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
                     acc = add3<X>(acc, ps.L);
                     ++sample;
-                    if (sample >= spp) {
-                        float* out = fp.fb + 3 * ((size_t)py * W + px);
+                    if (sample >= s_end) {
+                        float* out = (nchunks > 1 ? fp.part + (size_t)((sample - 1) / fp.chunk_spp) * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
                         out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
                         has_pixel = false;
                     }
@@ -86,9 +86,11 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     unsigned k = 0;
                     if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
                     k = __shfl_sync(full, k, 0);
-                    if ((int)(k / kBlocksPerTile) >= fp.my_tiles) { exhausted = true; break; }
-                    pool_tile = (int)(k / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
-                    pool_blk = (int)(k % kBlocksPerTile);
+                    const unsigned kb = k / (unsigned)nchunks;  // item = (tile, 8x4 block, sample chunk), chunk fastest
+                    if ((int)(kb / kBlocksPerTile) >= fp.my_tiles) { exhausted = true; break; }
+                    pool_tile = (int)(kb / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
+                    pool_blk = (int)(kb % kBlocksPerTile);
+                    pool_s0 = (int)(k % (unsigned)nchunks) * fp.chunk_spp;
                     pool_next = 0;
                 }
                 int avail = kBlockPixels - pool_next;
@@ -104,7 +106,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     } else if (x < W && y < H) {
                         has_pixel = true;
                         px = x; py = y;
-                        sample = 0;
+                        sample = pool_s0;
+                        s_end = min(spp, pool_s0 + fp.chunk_spp);
                         acc = mk3(0, 0, 0);
                         pixel_base = pixel_seed_base(x, y, W);
                     }
@@ -214,6 +217,29 @@ cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n
     if (blocks > 148 * 2 * 4) blocks = 148 * 2 * 4;
     if (blocks < 1) blocks = 1;
     trace_primary_kernel<<<blocks, threads, smem, stream>>>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- sum of the sample chunks (render_mega with nchunks > 1)
+__global__ void reduce_chunks_kernel(const __grid_constant__ FrameParams fp) {
+    const int W = fp.cam.W, H = fp.cam.H;
+    const size_t plane = (size_t)W * H * 3;
+    for (int k = blockIdx.x; k < fp.my_tiles; k += gridDim.x) {
+        int t = k * fp.tile_nranks + fp.tile_rank;
+        int x = (t % fp.tiles_x) * kTile + (threadIdx.x & 15), y = (t / fp.tiles_x) * kTile + (threadIdx.x >> 4);
+        if (x < W && y < H) {
+            size_t i = 3 * ((size_t)y * W + x);
+            float r = fp.part[i], g = fp.part[i + 1], b = fp.part[i + 2];
+            for (int c = 1; c < fp.nchunks; ++c) {
+                const float* p = fp.part + c * plane + i;
+                r += p[0]; g += p[1]; b += p[2];
+            }
+            fp.fb[i] = r; fp.fb[i + 1] = g; fp.fb[i + 2] = b;
+        }
+    }
+}
+cudaError_t launch_reduce_chunks(const FrameParams& fp, cudaStream_t stream) {
+    reduce_chunks_kernel<<<148 * 8, kTile * kTile, 0, stream>>>(fp);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,10 @@ struct FrameParams {
     int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
     int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
     float* fb;                        // W*H*3 sums
+    // sample chunks (render_mega only): a work item is (8x4 pixel block, chunk of chunk_spp samples); with nchunks > 1 a
+    // lane writes its chunk's partial sum to part[chunk][pixel] and reduce_chunks adds the chunks in order into fb
+    float* part;
+    int chunk_spp, nchunks;
     unsigned int* tile_counter;       // work queue head (zeroed before launch)
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
 };
@@ -57,6 +61,8 @@ cudaError_t launch_render_wavefront(const DevScene& sc, const FrameParams& fp, i
                                     WavefrontScratch& scratch, cudaStream_t stream);
 cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
                                  int* d_index, float* d_t, cudaStream_t stream);
+// fb[pixel] = part[0][pixel] + part[1][pixel] + ... (in chunk order: deterministic) for the pixels of this rank's tiles
+cudaError_t launch_reduce_chunks(const FrameParams& fp, cudaStream_t stream);
 cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, cudaStream_t stream);
 cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, cudaStream_t stream);
 cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, float* d_fb, cudaStream_t stream);

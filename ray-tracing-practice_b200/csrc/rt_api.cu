@@ -67,6 +67,8 @@ struct rt_scene {
     void* d_trace = nullptr;
     size_t trace_bytes = 0;
     WavefrontScratch wf;
+    float* d_part = nullptr;   // partial sums of the sample chunks (render_mega)
+    size_t part_floats = 0;
     bool pending = false;
     cudaStream_t pending_stream = nullptr;
 };
@@ -212,7 +214,7 @@ void rt_scene_destroy(rt_scene* s) {
     if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
     if (s->tex_array) cudaFreeArray(s->tex_array);
     void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
-                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf};
+                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_part};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (s->ev0) cudaEventDestroy(s->ev0);
@@ -234,6 +236,7 @@ static rt_render_opts resolve_opts(const rt_render_opts* in) {
     o.tex_mode = RT_TEX_GPU;
     o.top_nodes_in_smem = -1;
     o.tile_nranks = 1;
+    o.sample_chunk = 0;
     if (in) {
         size_t n = in->struct_size > 0 && (size_t)in->struct_size < sizeof o ? (size_t)in->struct_size : sizeof o;
         memcpy(&o, in, n);
@@ -243,6 +246,7 @@ static rt_render_opts resolve_opts(const rt_render_opts* in) {
             d.tex_mode = RT_TEX_GPU;
             d.top_nodes_in_smem = -1;
             d.tile_nranks = 1;
+            d.sample_chunk = 0;
             memcpy((char*)&o + n, (char*)&d + n, sizeof o - n);
         }
     }
@@ -270,6 +274,29 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     fp.fb = d_fb;
     fp.tile_counter = s->d_tile_counter;
     fp.counters = s->d_counters;
+    // sample chunks: shorter work items at the end of the frame (the tail is what limits strong scaling over GPUs).
+    // Only the production stream is chunked: parity mode keeps the reference's per-pixel summation order bit for bit.
+    fp.part = nullptr;
+    fp.chunk_spp = fp.cam.spp > 0 ? fp.cam.spp : 1;
+    fp.nchunks = 1;
+    int want_chunk = o.sample_chunk;
+    if (o.rng != RT_RNG_PHILOX) want_chunk = -1;
+    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 64) ? 32 : -1;
+    if (want_chunk > 0 && o.kernel == RT_KERNEL_MEGA && fp.cam.spp > want_chunk && fp.cam.depth > 0) {
+        int n = (fp.cam.spp + want_chunk - 1) / want_chunk;
+        if (n > 8) n = 8;
+        fp.chunk_spp = (fp.cam.spp + n - 1) / n;
+        fp.nchunks = (fp.cam.spp + fp.chunk_spp - 1) / fp.chunk_spp;
+        size_t need = (size_t)fp.nchunks * fp.cam.W * fp.cam.H * 3;
+        if (s->part_floats < need) {
+            if (s->d_part) cudaFree(s->d_part);
+            s->d_part = nullptr;
+            s->part_floats = 0;
+            RT_CUDA(cudaMalloc((void**)&s->d_part, need * sizeof(float)));
+            s->part_floats = need;
+        }
+        fp.part = s->d_part;
+    }
     DevScene dev = s->dev;
     int top = o.top_nodes_in_smem < 0 ? s->default_top : o.top_nodes_in_smem;
     if (top > dev.num_nodes) top = dev.num_nodes;
@@ -292,6 +319,7 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     if (o.kernel == RT_KERNEL_MEGA) RT_CUDA(launch_render_mega(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else if (o.kernel == RT_KERNEL_POOL) RT_CUDA(launch_render_pool(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else RT_CUDA(launch_render_wavefront(dev, fp, o.rng, o.exact_math, o.count_work, cfg, s->wf, stream));
+    if (fp.nchunks > 1) RT_CUDA(launch_reduce_chunks(fp, stream));
     RT_CUDA(cudaEventRecord(s->ev1, stream));
     s->pending = true;
     s->pending_stream = stream;

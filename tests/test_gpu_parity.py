@@ -243,3 +243,28 @@ def test_gpu_render_driver_writes_reference_format(rt, tmp_path):
     raw = np.fromfile(tmp_path / "o_1.png", np.uint8)
     assert list(np.frombuffer(raw[:8].tobytes(), np.int32)) == [64, 40] and len(raw) == 8 + 64 * 40 * 3
     assert raw[8:].max() > 0
+
+
+def test_sample_chunks_change_only_the_summation_grouping(rt, test_scene):
+    """megakernel work items split a pixel's samples into chunks (shorter end-of-frame tail): same samples, same segment
+    count, chunk sums added in chunk order => deterministic and equal to the unsplit frame up to fp32 re-association"""
+    sc, g = test_scene
+    cam = g["camera"].copy()
+    cam["samples_per_pixel"] = 100
+    whole, iw = sc.render(cam, seed=3, sample_chunk=-1, count_work=True)
+    for chunk in (16, 33, 64):
+        part, ip = sc.render(cam, seed=3, sample_chunk=chunk, count_work=True)
+        assert ip["segments"] == iw["segments"] and ip["samples"] == iw["samples"] == 200 * 100 * 100
+        assert np.allclose(part, whole, rtol=2e-5, atol=1e-5)
+        again, _ = sc.render(cam, seed=3, sample_chunk=chunk)
+        assert again.tobytes() == part.tobytes()
+    auto, _ = sc.render(cam, seed=3)                       # auto: 100 spp >= 64 -> chunks of 32 (4 chunks of 25)
+    assert np.allclose(auto, whole, rtol=2e-5, atol=1e-5) and auto.tobytes() != whole.tobytes()
+    acc = np.zeros_like(whole)
+    for r in range(2):                                      # chunked + tile partition: disjoint tiles, identical pixels
+        p, _ = sc.render(cam, seed=3, tile_rank=r, tile_nranks=2)
+        acc += p
+    assert acc.tobytes() == auto.tobytes()
+    ref, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, sample_chunk=16)   # parity mode is never split
+    ref2, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, sample_chunk=-1)
+    assert ref.tobytes() == ref2.tobytes()

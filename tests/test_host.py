@@ -31,7 +31,7 @@ def test_c_abi_exports_every_declared_symbol(rt):
 
 
 def test_struct_sizes_match_header(rt):
-    assert C.sizeof(rt.RenderOpts) == 48 and C.sizeof(rt.WorkCounters) == 48
+    assert C.sizeof(rt.RenderOpts) == 56 and C.sizeof(rt.WorkCounters) == 48
     assert rt.SPHERE.itemsize == 32 and rt.PLANE.itemsize == 80 and rt.MATERIAL.itemsize == 64 and rt.CAMERA.itemsize == 76
 
 
