@@ -281,10 +281,15 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     fp.nchunks = 1;
     int want_chunk = o.sample_chunk;
     if (o.rng != RT_RNG_PHILOX) want_chunk = -1;
-    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 64) ? 32 : -1;
+    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 8 : -1;
     if (want_chunk > 0 && o.kernel == RT_KERNEL_MEGA && fp.cam.spp > want_chunk && fp.cam.depth > 0) {
         int n = (fp.cam.spp + want_chunk - 1) / want_chunk;
-        if (n > 8) n = 8;
+        // the partial-sum planes are capped at 32 chunks and ~3.2 GB (8 planes of an 8K frame)
+        size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
+        int cap = (int)((size_t)3300000000ull / plane_bytes);
+        if (cap > 32) cap = 32;
+        if (cap < 1) cap = 1;
+        if (n > cap) n = cap;
         fp.chunk_spp = (fp.cam.spp + n - 1) / n;
         fp.nchunks = (fp.cam.spp + fp.chunk_spp - 1) / fp.chunk_spp;
         size_t need = (size_t)fp.nchunks * fp.cam.W * fp.cam.H * 3;

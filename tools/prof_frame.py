@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--count", action="store_true")
     ap.add_argument("--top-nodes", type=int, default=-1)
     ap.add_argument("--frame", type=int, default=0)
+    ap.add_argument("--chunk", type=int, default=0, help="sample_chunk option (0 auto, -1 whole pixels)")
     a = ap.parse_args()
     cfg = rt.CONFIGS[a.workload]
     hs = rt.synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
@@ -34,7 +35,7 @@ def main():
         cam["max_depth"] = a.depth
     fb = np.zeros((cfg["H"], cfg["W"], 3), np.float32)
     kw = dict(kernel={"mega": rt.KERNEL_MEGA, "wavefront": rt.KERNEL_WAVEFRONT, "pool": rt.KERNEL_POOL}[a.kernel],
-              rng=rt.RNG_PHILOX if a.rng == "philox" else rt.RNG_REFERENCE, exact=a.exact, top_nodes=a.top_nodes)
+              rng=rt.RNG_PHILOX if a.rng == "philox" else rt.RNG_REFERENCE, exact=a.exact, top_nodes=a.top_nodes, sample_chunk=a.chunk)
     best = None
     for _ in range(a.reps):
         _, info = scene.render(cam, out=fb, **kw)
