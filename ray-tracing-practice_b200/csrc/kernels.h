@@ -39,7 +39,7 @@ constexpr int kBlocksPerTile = kTile * kTile / kBlockPixels;
 #define RTB_MEGA_THREADS 256
 #endif
 #ifndef RTB_MEGA_BLOCKS
-#define RTB_MEGA_BLOCKS 2
+#define RTB_MEGA_BLOCKS 3
 #endif
 constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of the persistent kernels
 constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM they are compiled (register-capped) for

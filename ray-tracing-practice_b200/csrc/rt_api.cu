@@ -303,7 +303,8 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
         fp.part = s->d_part;
     }
     DevScene dev = s->dev;
-    int top = o.top_nodes_in_smem < 0 ? s->default_top : o.top_nodes_in_smem;
+    // megakernel default: no staging (measured no gain); the other kernels keep the 64-node default
+    int top = o.top_nodes_in_smem < 0 ? (o.kernel == RT_KERNEL_MEGA ? 0 : s->default_top) : o.top_nodes_in_smem;
     if (top > dev.num_nodes) top = dev.num_nodes;
     if (top > 1024) top = 1024;
     dev.top_nodes = top;

@@ -200,12 +200,12 @@ __device__ __forceinline__ void trav_pop(RayTrav& r, const TravStack& stk) {
 // caller pops); otherwise r.ref is the nearest child and the others are on the stack, far to near.
 // The near / far plane of each axis is chosen by the LOAD ADDRESS (per-ray constants nx, ny, nz), not by min/max of
 // both products; empty slots hold lo = +inf, hi = -inf and fail the test on their own.
-template <bool X, bool COUNT>
+template <bool X, bool COUNT, bool TOP = true>
 __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __restrict__ s_top, const TravStack& stk, RayTrav& r,
                                            WorkCount& wc) {
     const int ref = r.ref;
     float4 nx4, ny4, nz4, fx4, fy4, fz4, c;
-    if (ref < sc.top_nodes) {
+    if (TOP && ref < sc.top_nodes) {
         const float4* p = s_top + ref * kTopStride;
         nx4 = p[r.nx]; ny4 = p[r.ny]; nz4 = p[r.nz]; fx4 = p[3 - r.nx]; fy4 = p[5 - r.ny]; fz4 = p[7 - r.nz];
         c = p[6];
@@ -272,14 +272,22 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
             h = plane_t<X>(r.o, r.d, sc.planes + 5 * (size_t)(first + k), r.tmin, r.closest, t, al, be);
         }
         if (h) {
-            int orig = type == 0 ? __ldg(sc.sphere_meta + first + k).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)(first + k) + 3).w);
-            unsigned int key = ((unsigned int)type << 30) | (unsigned int)orig;
-            if (t < r.closest || r.htype < 0 || key > r.best_key) {
+            if (X) {
+                // exact mode reproduces the reference's tie rule (t == closest: the later primitive in array order wins)
+                int orig = type == 0 ? __ldg(sc.sphere_meta + first + k).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)(first + k) + 3).w);
+                unsigned int key = ((unsigned int)type << 30) | (unsigned int)orig;
+                if (t < r.closest || r.htype < 0 || key > r.best_key) {
+                    r.closest = t;
+                    r.best_key = key;
+                    r.htype = type;
+                    r.hslot = first + k;
+                    r.horig = orig;
+                }
+            } else {
+                // production: exact ties have measure zero; no caller's index, no key (two registers and a load less)
                 r.closest = t;
-                r.best_key = key;
                 r.htype = type;
                 r.hslot = first + k;
-                r.horig = orig;
             }
         }
     }
@@ -313,6 +321,8 @@ __device__ __forceinline__ void trace_closest(const DevScene& sc, const float4* 
         if (pop) trav_pop(r, stk);
     }
     hit = trav_hit(r);
+    if (!X && r.htype >= 0)  // fast mode does not carry the caller's index through the traversal: one lookup at the end
+        hit.orig = r.htype == 0 ? __ldg(sc.sphere_meta + r.hslot).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)r.hslot + 3).w);
 }
 
 }  // namespace rtb
