@@ -1,3 +1,4 @@
+#include <cstdlib>
 // wide_bvh.cpp -- binned-SAH build + collapse to 128-byte 4-wide nodes (see wide_bvh.h).
 // Stands where the reference's build_bvh / build_bvh_recursive stand (include/bvh_builder.h:52-120); nothing of
 // their median-split algorithm is kept -- the tree quality (Q4 in SURVEY.md: ~100 node visits per ray) is what
@@ -17,7 +18,11 @@ namespace {
 
 constexpr int kBins = 16;
 constexpr float kCostNode = 1.0f;  // one wide-node visit (8 x LDG.128 + 4 slab tests)
-constexpr float kCostPrim = 0.5f;  // one leaf primitive test
+static float cost_prim_value() {
+    const char* e = getenv("RTB_COST_PRIM");  // tuning knob for profiling runs
+    return e ? (float)atof(e) : 0.5f;
+}
+static const float kCostPrim = cost_prim_value();  // one leaf primitive test, in units of a wide-node visit
 
 struct Box3 {
     float lo[3], hi[3];
