@@ -287,7 +287,7 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
         // the partial-sum planes are capped at 32 chunks and ~3.2 GB (8 planes of an 8K frame)
         size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
         int cap = (int)((size_t)3300000000ull / plane_bytes);
-        if (cap > 32) cap = 32;
+        if (cap > 128) cap = 128;
         if (cap < 1) cap = 1;
         if (n > cap) n = cap;
         fp.chunk_spp = (fp.cam.spp + n - 1) / n;

@@ -172,7 +172,11 @@ __device__ __forceinline__ void trav_begin(RayTrav& r, V3 o, V3 d, float tmin, f
     r.tmin = tmin;
     r.closest = tmax;
     // conservative slab test: the far side is widened by a few ulps of the slab products (boxes are padded too)
-    r.eps = 1e-7f * (fabsf(r.oox) + fabsf(r.ooy) + fabsf(r.ooz));
+    // Each axis contributes the rounding error of its own slab products, CAPPED: for an axis the ray is (almost) parallel
+    // to, id = 1e20 and o*id = 1e21 -- its products decide nothing unless the origin sits within 1e-6 of a box face, but
+    // uncapped they would widen the test so much that such a ray visits every box its origin plane cuts (measured: one
+    // such ray in ~4e6 (sincospi gives exact zeros) cost 15 ms, the whole tail of a frame).
+    r.eps = 1e-7f * (fminf(fabsf(r.oox), 1e3f) + fminf(fabsf(r.ooy), 1e3f) + fminf(fabsf(r.ooz), 1e3f));
     r.nx = dx < 0.0f ? 3 : 0;
     r.ny = dy < 0.0f ? 4 : 1;
     r.nz = dz < 0.0f ? 5 : 2;
