@@ -374,6 +374,40 @@ def test_config_text(W=200, H=100, fov=90, max_depth=5, sqrt_spp=2, texture="../
     return "\n".join(lines) + "\n"
 
 
+def shipped_config_text(W=1080, H=720, fov=50, max_depth=50, sqrt_spp=50, texture="../floor2.jpg", output="render_%d.png",
+                        num_frames=100):
+    """The token stream of the reference's shipped config.txt (config.txt:1-17; BASELINE.json configs[0]): three glass
+    solids, floor quad, four lights, camera on the cylindrical path of src/camera.cu:301-315.  Output path and texture
+    tokens are parameters because the shipped ones point at the author's machine / a missing file."""
+    lines = [str(num_frames), output, "%d %d %g" % (W, H, fov),
+             "15.0 4.5 3.14159    0.0 4.5    0.0 1.0 1.0    0.0 -1.57",
+             "0.0 4.5 0.0    0.0 4.5    0.0 1.0 0.0    0.0 -1.57",
+             "0.0 0.0 3.0     0.3 0.0 0.0     3.0     1.5     0.1     3",
+             "4 0.0 6.0     0.0 0.3 0.0     3.0     1.2     0.1     2",
+             "8 0.0 9.0     0.0 0.0 0.3     3.0     1     0.1     1",
+             "-15.0 -15.0 -1.0      -15.0 15.0 -1.0       15.0 15.0 -1.0        15.0 -15.0 -1.0 " + texture,
+             "1.0 1.0 1.0", "0.3", "4",
+             "-15.0 -15.0 1  10.0 10.0 10.0", "-15.0 15.0 1   10.0 10.0 10.0",
+             "15.0 15.0 1    10.0 10.0 10.0", "15.0 -15.0 1   10.0 10.0 10.0",
+             "%d %d" % (max_depth, sqrt_spp)]
+    return "\n".join(lines) + "\n"
+
+
+def synthetic_texture(w=2000, h=1330, seed=7):
+    """A float RGBA texture of floor.jpg's shape (2000x1330) for runs on boxes where the reference's asset is absent:
+    linear-light checker + seeded noise, alpha 1 -- the layout stbi_loadf(..., 4) returns (src/main.cu:18)."""
+    rng = np.random.default_rng(seed)
+    yy, xx = np.mgrid[0:h, 0:w]
+    chk = (((xx // 125) + (yy // 95)) & 1).astype(np.float32)
+    tex = np.empty((h, w, 4), np.float32)
+    tex[..., 0] = 0.15 + 0.6 * chk
+    tex[..., 1] = 0.2 + 0.5 * (1 - chk)
+    tex[..., 2] = 0.25 + 0.1 * chk
+    tex[..., :3] *= (0.85 + 0.3 * rng.random((h, w, 1), dtype=np.float32))
+    tex[..., 3] = 1.0
+    return tex
+
+
 # the synthetic configs of BASELINE.json (SURVEY.md section 8d): create_test_config.py scene + N seeded spheres
 CONFIGS = {
     "test_config_200x100": dict(n=0, W=200, H=100, sqrt_spp=2, depth=5),
