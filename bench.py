@@ -231,7 +231,7 @@ def main():
         segs_all = float(segs)
     value = segs_all / (ms_total * 1e-3) / 1e6
     if args.kernel == "mega":
-        chunked = spp >= 32 and spp > 8  # rt_render_opts.sample_chunk auto: render_mega + reduce_chunks
+        chunked = spp >= 32  # rt_render_opts.sample_chunk auto: render_mega + reduce_chunks
         launches_per_step = 1 + (1 if chunked else 0) + (1 if world > 1 else 0) + (1 if (world > 1 and rank == 0) else 0)  # render, reduce, pack, unpack(rank 0)
     else:
         K = max(1, min(spp, (16 << 20) // max(1, ((W + 15) // 16) * ((H + 15) // 16) * 256 // world)))

@@ -53,8 +53,8 @@ typedef struct rt_render_opts {
                                    nranks <= 1 renders everything.  Pixels of other ranks are left untouched. */
     int count_work;             /* 1: also count node visits / leaf tests / shaded hits (slower; for the roofline) */
     int top_nodes_in_smem;      /* -1 default (megakernel: 0, others: 64); 0 off; N>0: stage the first N wide nodes in shared memory */
-    int sample_chunk;           /* megakernel work-item length in samples: 0 auto (8 for the Philox stream when spp >= 32, at most
-                                   32 chunks per pixel and ~3.2 GB of partial sums; chunk sums are added in chunk order, so the frame stays deterministic);
+    int sample_chunk;           /* megakernel work-item length in samples: 0 auto (2 for the Philox stream when spp >= 32, at most
+                                   128 chunks per pixel and ~3.3 GB of partial sums; chunk sums are added in chunk order, so the frame stays deterministic);
                                    -1 never split a pixel (always the case for RT_RNG_REFERENCE: the reference's summation order) */
 } rt_render_opts;
 

@@ -281,10 +281,10 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     fp.nchunks = 1;
     int want_chunk = o.sample_chunk;
     if (o.rng != RT_RNG_PHILOX) want_chunk = -1;
-    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 8 : -1;
+    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 2 : -1;
     if (want_chunk > 0 && o.kernel == RT_KERNEL_MEGA && fp.cam.spp > want_chunk && fp.cam.depth > 0) {
         int n = (fp.cam.spp + want_chunk - 1) / want_chunk;
-        // the partial-sum planes are capped at 32 chunks and ~3.2 GB (8 planes of an 8K frame)
+        // the partial-sum planes are capped at 128 chunks and ~3.3 GB (128 planes of a 1080p frame, 8 of an 8K frame)
         size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
         int cap = (int)((size_t)3300000000ull / plane_bytes);
         if (cap > 128) cap = 128;

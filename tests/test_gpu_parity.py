@@ -258,7 +258,7 @@ def test_sample_chunks_change_only_the_summation_grouping(rt, test_scene):
         assert np.allclose(part, whole, rtol=2e-5, atol=1e-5)
         again, _ = sc.render(cam, seed=3, sample_chunk=chunk)
         assert again.tobytes() == part.tobytes()
-    auto, _ = sc.render(cam, seed=3)                       # auto: 100 spp >= 32 -> chunks of 8 (13 chunks)
+    auto, _ = sc.render(cam, seed=3)                       # auto: 100 spp >= 32 -> chunks of 2 (50 chunks)
     assert np.allclose(auto, whole, rtol=2e-5, atol=1e-5) and auto.tobytes() != whole.tobytes()
     acc = np.zeros_like(whole)
     for r in range(2):                                      # chunked + tile partition: disjoint tiles, identical pixels
