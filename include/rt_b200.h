@@ -106,6 +106,11 @@ int rt_trace_primary(rt_scene* scene, const float* rays6, int num_rays, float tm
  * (unsigned char)(256*clamp(sqrt(sum/divisor),0,0.999)).  d_fb_sum_rgb is a device pointer, rgb_u8 a host one. */
 int rt_tonemap_u8(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int divisor, unsigned char* rgb_u8);
 
+/* rt_render followed by the output stage without the float download: replaces Camera::render + the per-pixel
+ * saver->writeColor loop (src/camera.cu:198-215).  rgb_u8 is a HOST buffer of W*H*3 bytes, row-major. */
+int rt_render_u8(rt_scene* scene, const void* camera_data76, const rt_render_opts* opts, int divisor, unsigned char* rgb_u8,
+                 unsigned long long* ray_segments, float* kernel_ms);
+
 /* Tile partition helpers for the multi-GPU frame (tiles are RT_TILE x RT_TILE pixels, row-major tile ids). */
 #define RT_TILE 16
 int rt_tiles_pack(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int rank, int nranks, void* d_packed,

@@ -38,7 +38,7 @@ TEX_CPU, TEX_GPU = 0, 1
 TILE = 16
 
 C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
-                 "rt_render_finish", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
+                 "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
                  "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_version"]
 
 
@@ -90,6 +90,7 @@ def lib():
         L.rt_render.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.rt_render_device.argtypes = [vp, vp, vp, vp, vp]
         L.rt_render_finish.argtypes = [vp, vp, vp, vp]
+        L.rt_render_u8.argtypes = [vp, vp, vp, ci, vp, vp, vp]
         L.rt_trace_primary.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp]
         L.rt_tonemap_u8.argtypes = [vp, vp, ci, ci, ci, vp]
         L.rt_tiles_pack.argtypes = [vp, vp, ci, ci, ci, ci, vp, vp]
@@ -301,6 +302,16 @@ class Scene:
         info = {n: getattr(wc, n) for n, _ in WorkCounters._fields_}
         info.update(segments=segs.value, kernel_ms=ms.value)
         return fb, info
+
+    def render_u8(self, cam, divisor, **kw):
+        """One frame through rt_render_u8: render + device-side output stage; returns (uint8 [H,W,3], info)."""
+        cam = np.ascontiguousarray(cam, CAMERA)
+        W, H = int(cam["image_width"][0]), int(cam["image_height"][0])
+        out = np.zeros((H, W, 3), np.uint8)
+        o = self._opts(**kw)
+        segs, ms = C.c_ulonglong(), C.c_float()
+        _check(lib().rt_render_u8(self.h, _ptr(cam), C.byref(o), int(divisor), _ptr(out), C.byref(segs), C.byref(ms)))
+        return out, dict(segments=segs.value, kernel_ms=ms.value)
 
     def render_device(self, cam, d_fb_ptr, stream=None, **kw):
         cam = np.ascontiguousarray(cam, CAMERA)

@@ -378,6 +378,30 @@ int rt_render(rt_scene* s, const void* cam76, const rt_render_opts* opts, float*
     return RT_OK;
 }
 
+// render + device-side output stage: the frame never leaves the GPU as floats (3 B/pixel D2H instead of 12)
+int rt_render_u8(rt_scene* s, const void* cam76, const rt_render_opts* opts, int divisor, unsigned char* rgb,
+                 unsigned long long* segs, float* kernel_ms) {
+    if (!s || !cam76 || !rgb || divisor <= 0) return fail(RT_ERR_INVALID, "rt_render_u8: bad argument");
+    CameraPod cam;
+    memcpy(&cam, cam76, sizeof cam);
+    if (cam.W <= 0 || cam.H <= 0) return fail(RT_ERR_INVALID, "rt_render_u8: bad CameraData");
+    size_t n = (size_t)cam.W * cam.H * 3;
+    if (s->fb_floats < n) {
+        if (s->d_fb) cudaFree(s->d_fb);
+        s->d_fb = nullptr;
+        s->fb_floats = 0;
+        RT_CUDA(cudaMalloc((void**)&s->d_fb, n * sizeof(float)));
+        s->fb_floats = n;
+    }
+    rt_render_opts o = resolve_opts(opts);
+    if (o.tile_nranks > 1) RT_CUDA(cudaMemsetAsync(s->d_fb, 0, n * sizeof(float), s->stream));
+    int rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
+    if (rc) return rc;
+    rc = rt_render_finish(s, segs, kernel_ms, nullptr);
+    if (rc) return rc;
+    return rt_tonemap_u8(s, nullptr, cam.W, cam.H, divisor, rgb);
+}
+
 int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float tmax, int* type, int* index, float* t) {
     if (!s || (n > 0 && (!rays6 || !type || !index || !t)) || n < 0) return fail(RT_ERR_INVALID, "rt_trace_primary: bad argument");
     if (n == 0) return RT_OK;

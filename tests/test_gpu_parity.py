@@ -268,3 +268,17 @@ def test_sample_chunks_change_only_the_summation_grouping(rt, test_scene):
     ref, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, sample_chunk=16)   # parity mode is never split
     ref2, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, sample_chunk=-1)
     assert ref.tobytes() == ref2.tobytes()
+
+
+def test_render_u8_is_render_plus_reference_output_stage(rt, test_scene):
+    """rt_render_u8 = rt_render + ISaver::writeColor arithmetic (src/camera.cu:136-148) on the device, byte for byte"""
+    sc, g = test_scene
+    cam = g["camera"]
+    fb, info = sc.render(cam, seed=9)
+    for divisor in (1, 2, 4):
+        u8, iu = sc.render_u8(cam, divisor, seed=9)
+        assert iu["segments"] == info["segments"]
+        assert u8.tobytes() == rt.tonemap_host(fb, divisor).tobytes()
+    ref, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    u8, _ = sc.render_u8(cam, 2, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    assert u8.tobytes() == rt.tonemap_host(g["fb_sum"], 2).tobytes() or (u8 != rt.tonemap_host(g["fb_sum"], 2)).mean() < 1e-3
