@@ -34,8 +34,15 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     float lst[kLocalStack];
     int lsr[kLocalStack];
     TravStack stk;
-    stk.st = ts.st; stk.sr = ts.sr; stk.lt = lst; stk.lr = lsr;
-    stk.tid = threadIdx.x; stk.nt = blockDim.x;
+    stk.lt = lst; stk.lr = lsr;
+    stk.tid = threadIdx.x;
+    stk.nt = kMegaThreads;  // launch geometry is fixed: constant strides, no rematerialised address math in push / pop
+    if (TOP) {
+        stk.st = ts.st; stk.sr = ts.sr;
+    } else {  // nothing staged: the stack sits at the start of dynamic shared memory, at compile-time offsets
+        stk.st = reinterpret_cast<float*>(smem4);
+        stk.sr = reinterpret_cast<int*>(smem4) + kSmemStack * kMegaThreads;
+    }
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -43,7 +50,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     const int leaf_min = fp.leaf_min, nchunks = fp.nchunks;
 
     // warp-uniform tile pool
-    int pool_tile = 0, pool_blk = 0, pool_s0 = 0, pool_next = kBlockPixels;
+    int pool_x0 = 0, pool_y0 = 0, pool_chunk = 0, pool_next = kBlockPixels;
     bool exhausted = false;
 
     // per-lane state
@@ -51,7 +58,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     trav_begin<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
     rt.ref = kRefNeed;
     bool has_pixel = false;
-    int px = 0, py = 0, sample = 0, s_end = 0;
+    int px = 0, py = 0, sample = 0, chunk = 0;
     PathState ps;
     ps.o = mk3(0, 0, 0); ps.d = mk3(0, 0, 1); ps.beta = mk3(1, 1, 1); ps.L = mk3(0, 0, 0); ps.depth = 0;
     V3 acc = mk3(0, 0, 0);
@@ -71,8 +78,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
                     acc = add3<X>(acc, ps.L);
                     ++sample;
-                    if (sample >= s_end) {
-                        float* out = (nchunks > 1 ? fp.part + (size_t)((sample - 1) / fp.chunk_spp) * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
+                    if (sample >= min(spp, (chunk + 1) * fp.chunk_spp)) {
+                        float* out = (nchunks > 1 ? fp.part + (size_t)chunk * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
                         out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
                         has_pixel = false;
                     }
@@ -90,26 +97,27 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     k = __shfl_sync(full, k, 0);
                     const unsigned kb = k / (unsigned)nchunks;  // item = (tile, 8x4 block, sample chunk), chunk fastest
                     if ((int)(kb / kBlocksPerTile) >= fp.my_tiles) { exhausted = true; break; }
-                    pool_tile = (int)(kb / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
-                    pool_blk = (int)(kb % kBlocksPerTile);
-                    pool_s0 = (int)(k % (unsigned)nchunks) * fp.chunk_spp;
+                    const int tile = (int)(kb / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
+                    const int blk = (int)(kb % kBlocksPerTile);  // 8 blocks of 8x4 pixels inside the 16x16 tile
+                    pool_x0 = (tile % fp.tiles_x) * kTile + (blk & 1) * 8;
+                    pool_y0 = (tile / fp.tiles_x) * kTile + (blk >> 1) * 4;
+                    pool_chunk = (int)(k % (unsigned)nchunks);
                     pool_next = 0;
                 }
                 int avail = kBlockPixels - pool_next;
                 int rank = __popc(need & ((1u << lane) - 1u));
                 if (rt.ref == kRefNeed && !has_pixel && rank < avail) {
                     int q = pool_next + rank;
-                    int blk = pool_blk;  // 8 blocks of 8x4 pixels inside the 16x16 tile
-                    int x = (pool_tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
-                    int y = (pool_tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + (q >> 3);
+                    int x = pool_x0 + (q & 7);
+                    int y = pool_y0 + (q >> 3);
                     if (x < W && y < H && (spp <= 0 || fp.cam.depth <= 0)) {
                         float* out = fp.fb + 3 * ((size_t)y * W + x);  // no samples / no segments: the pixel is black
                         out[0] = 0.f; out[1] = 0.f; out[2] = 0.f;
                     } else if (x < W && y < H) {
                         has_pixel = true;
                         px = x; py = y;
-                        sample = pool_s0;
-                        s_end = min(spp, pool_s0 + fp.chunk_spp);
+                        chunk = pool_chunk;
+                        sample = pool_chunk * fp.chunk_spp;
                         acc = mk3(0, 0, 0);
                         pixel_base = pixel_seed_base(x, y, W);
                     }
