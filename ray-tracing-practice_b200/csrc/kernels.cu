@@ -10,11 +10,10 @@
 //          max_depth); a lane whose pixel is complete takes the next pixel of the warp's current work item.  Work
 //          items are 8x4-pixel blocks of the 16x16 tiles, fetched with ONE atomicAdd per warp (lane 0) and a shuffle
 //          broadcast; ballot/popc ranks hand the pixels to the lanes that need one.
-//   TRACE  a while-while traversal of the 32 segments: each iteration the warp votes (ballot/popc); lanes holding an
-//          inner node visit it, lanes holding a leaf wait until `leaf_min` of them have gathered (or no inner node is
-//          left) so the primitive tests run together instead of once per lane inside the node loop.
-// Measured alternatives that lost and why are in DESIGN.md: letting lanes leave the phase (shade as soon as k lanes
-// are done) and the pooled variant (mega_pool.cu) raise lane occupancy of the shading code but run 10-45 % slower.
+//   TRACE  every lane runs the closest-hit traversal of its segment (4-wide BVH, near-first, per-thread stack in local
+//          memory) to completion; the warp re-converges for the next SHADE phase.
+// Measured alternatives that lost and why are in DESIGN.md 4.2: a shared-memory stack, warp votes inside the traversal,
+// lanes leaving the phase early, pre-tracing the next camera ray in idle lanes, and the pooled variant (mega_pool.cu).
 // Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored once,
 // so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
@@ -31,10 +30,9 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     extern __shared__ float4 smem4[];
     const TraversalSmem ts = carve_and_stage(sc, smem4);
     const float4* s_top = ts.top;
-    float lst[kLocalStack];
-    int lsr[kLocalStack];
+    float2 lstack[kLocalStack];
     TravStack stk;
-    stk.lt = lst; stk.lr = lsr;
+    stk.lo = lstack;
     stk.tid = threadIdx.x;
     stk.nt = kMegaThreads;  // launch geometry is fixed: constant strides, no rematerialised address math in push / pop
     if (TOP) {
@@ -47,7 +45,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int W = fp.cam.W, H = fp.cam.H, spp = fp.cam.spp;
-    const int leaf_min = fp.leaf_min, nchunks = fp.nchunks;
+    const int nchunks = fp.nchunks;
 
     // warp-uniform tile pool
     int pool_x0 = 0, pool_y0 = 0, pool_chunk = 0, pool_next = kBlockPixels;
@@ -139,22 +137,14 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             if (start_ray) trav_begin<X>(rt, ps.o, ps.d, 0.001f, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
         }
         if (__all_sync(full, rt.ref == kRefIdle)) break;  // no pixels left for any lane
-        // ================= TRACE phase: while-while traversal of the warp's 32 segments.  Inner nodes are visited by
-        // every lane that holds one; lanes that reach a leaf wait until `leaf_min` of them have gathered (or nobody has
-        // an inner node left), so the primitive tests run with many lanes instead of once per lane per iteration.
-        for (;;) {
-            const unsigned lmask = __ballot_sync(full, ref_is_leaf(rt.ref));
-            const unsigned imask = __ballot_sync(full, ref_is_inner(rt.ref));
-            if ((lmask | imask) == 0u) break;
-            if (lmask != 0u && (__popc(lmask) >= leaf_min || imask == 0u)) {
-                if (ref_is_leaf(rt.ref)) {
-                    trav_leaf<X, COUNT>(sc, rt, wc);
-                    trav_pop(rt, stk);
-                }
-            }
-            if (ref_is_inner(rt.ref)) {
-                if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
-            }
+        // ================= TRACE phase: every lane runs its segment's closest-hit traversal to completion (traverse.cuh).
+        // Measured on B200: warp votes that batch the leaf tests (lanes wait until k hold a leaf) cost more than they save
+        // once the stack is in local memory -- the plain per-lane loop is 4-8 % faster than any vote threshold.
+        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
+            bool pop = true;
+            if (ref_is_leaf(rt.ref)) trav_leaf<X, COUNT>(sc, rt, wc);
+            else pop = trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc);
+            if (pop) trav_pop(rt, stk);
         }
     }
 

@@ -129,10 +129,9 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
     extern __shared__ float4 smem4[];
     const TraversalSmem ts = carve_and_stage(sc, smem4);
     const float4* s_top = ts.top;
-    float lst[kLocalStack];
-    int lsr[kLocalStack];
+    float2 lstack[kLocalStack];
     TravStack stk;
-    stk.st = ts.st; stk.sr = ts.sr; stk.lt = lst; stk.lr = lsr;
+    stk.st = ts.st; stk.sr = ts.sr; stk.lo = lstack;
     stk.tid = threadIdx.x; stk.nt = blockDim.x;
 
     const unsigned full = 0xffffffffu;

@@ -312,7 +312,6 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     // scheduling thresholds of the megakernels; the RTB_* variables are tuning knobs for profiling runs
     fp.leaf_min = kLeafMinDefault;
     if (const char* e = getenv("RTB_LEAF_MIN")) fp.leaf_min = atoi(e);
-    if (fp.leaf_min < 1) fp.leaf_min = 1;
     fp.refill_min = 32;
     fp.park_min = 32;
     if (const char* e = getenv("RTB_REFILL_MIN")) fp.refill_min = atoi(e);
