@@ -17,6 +17,12 @@
 // Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored once,
 // so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
+#ifndef RTB_LOOP_SHAPE
+#define RTB_LOOP_SHAPE 1
+#endif
+#ifndef RTB_LEAF_K
+#define RTB_LEAF_K 12
+#endif
 #include "path.cuh"
 #include "smem_top.cuh"
 
@@ -140,12 +146,62 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         // ================= TRACE phase: every lane runs its segment's closest-hit traversal to completion (traverse.cuh).
         // Measured on B200: warp votes that batch the leaf tests (lanes wait until k hold a leaf) cost more than they save
         // once the stack is in local memory -- the plain per-lane loop is 4-8 % faster than any vote threshold.
+#if RTB_LOOP_SHAPE == 0
         while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
             bool pop = true;
             if (ref_is_leaf(rt.ref)) trav_leaf<X, COUNT>(sc, rt, wc);
             else pop = trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc);
             if (pop) trav_pop(rt, stk);
         }
+#elif RTB_LOOP_SHAPE == 1
+        // one iteration = (leaf + pop)? then (inner node)?: a lane whose leaf test pops an inner node visits it in the same
+        // iteration, together with the lanes that were at inner nodes anyway
+        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
+            if (ref_is_leaf(rt.ref)) {
+                trav_leaf<X, COUNT>(sc, rt, wc);
+                trav_pop(rt, stk);
+            }
+            if (ref_is_inner(rt.ref)) {
+                if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+            }
+        }
+#elif RTB_LOOP_SHAPE == 3
+        // speculative traversal: a lane that reaches a leaf postpones it (one slot) and goes on with its next node; the
+        // postponed leaves of the whole warp are tested together when a lane reaches its second leaf, when RTB_LEAF_K lanes
+        // hold one, or when no lane has a node left
+        {
+            int pend = 0;
+            for (;;) {
+                if (ref_is_inner(rt.ref)) {
+                    if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+                }
+                if (ref_is_leaf(rt.ref) && pend == 0) {
+                    pend = rt.ref;
+                    trav_pop(rt, stk);
+                }
+                const unsigned int ib = __ballot_sync(full, ref_is_inner(rt.ref)), mb = __ballot_sync(full, ref_is_leaf(rt.ref));
+                const unsigned int pb = __ballot_sync(full, pend != 0);
+                if (mb != 0u || ib == 0u || __popc(pb) >= RTB_LEAF_K) {
+                    if (pend != 0) {
+                        trav_leaf<X, COUNT>(sc, rt, wc, pend);
+                        pend = 0;
+                    }
+                }
+                if ((ib | mb) == 0u) break;
+            }
+        }
+#else
+        // inner first, then leaf
+        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
+            if (ref_is_inner(rt.ref)) {
+                if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+            }
+            if (ref_is_leaf(rt.ref)) {
+                trav_leaf<X, COUNT>(sc, rt, wc);
+                trav_pop(rt, stk);
+            }
+        }
+#endif
     }
 
     // ---- work counters: warp reduce, one atomic per warp and counter

@@ -12,7 +12,7 @@ PackedScene pack_scene(const SphereIn* sp, int S, const PlaneIn* pl, int P, cons
     PackedScene ps;
     auto t0 = std::chrono::steady_clock::now();
     std::vector<PrimBox> prims = make_prim_boxes(sp, S, pl, P);
-    ps.bvh = build_wide_bvh(prims, 4);
+    ps.bvh = build_wide_bvh(prims, kMaxLeafPrims);
     ps.build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     const WideBvh& bvh = ps.bvh;
     ps.spheres.resize(bvh.sphere_order.size() * 4);

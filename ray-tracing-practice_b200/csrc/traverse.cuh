@@ -13,6 +13,7 @@
 //     later one in (spheres, then planes) array order.
 #pragma once
 #include "device_math.cuh"
+#include "leaf_size.h"
 
 namespace rtb {
 
@@ -37,6 +38,12 @@ struct DevScene {
 // the first design; measured on B200 it is 10 % SLOWER than all-local (two LDS/STS + address math + a shared/local branch
 // per push and pop, and it takes L1 capacity away from the nodes), so the default is 0.  The builder guarantees
 // max_stack <= 64.
+#ifndef RTB_TOPREG
+#define RTB_TOPREG 0
+#endif
+#ifndef RTB_LEAF_PRELOAD
+#define RTB_LEAF_PRELOAD 0
+#endif
 constexpr int kSmemStack = RTB_SMEM_STACK;
 constexpr int kLocalStack = 64 - kSmemStack;
 constexpr int kTopStride = 9;    // float4 per staged node: 8 + 1 pad (144 B) so 128-bit LDS spread over banks
@@ -143,6 +150,10 @@ struct RayTrav {
     int ref, sp;
     int htype, hslot, horig;             // closest hit so far: -1 miss / 0 sphere / 1 plane, re-ordered slot, caller's index
     unsigned int best_key;
+#if RTB_TOPREG
+    float top_t;                         // copy of the top stack entry: a pop never waits for its own load
+    int top_r;
+#endif
 };
 
 // per-thread stack: kSmemStack entries in shared memory (strided by the block size), the rest in local memory as
@@ -200,7 +211,12 @@ __device__ __forceinline__ void trav_pop(RayTrav& r, const TravStack& stk) {
         --r.sp;
         float t;
         int e;
+#if RTB_TOPREG
+        t = r.top_t; e = r.top_r;
+        if (r.sp > 0) stk.load(r.sp - 1, r.top_t, r.top_r);
+#else
         stk.load(r.sp, t, e);
+#endif
         if (t <= r.closest) { r.ref = e; break; }
     }
 }
@@ -258,6 +274,9 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
             ++r.sp;
         }
     }
+#if RTB_TOPREG
+    if (tn[1] < inf) { r.top_t = tn[1]; r.top_r = cr[1]; }
+#endif
     if (tn[0] < inf) {
         r.ref = cr[0];
         return false;
@@ -267,9 +286,28 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
 
 // one leaf: up to 4 same-type primitives; the caller pops afterwards
 template <bool X, bool COUNT>
-__device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc) {
-    unsigned int bits = (unsigned int)r.ref;
-    int type = (bits >> 30) & 1, cnt = ((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
+__device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc, int leaf_ref) {
+    unsigned int bits = (unsigned int)leaf_ref;
+    const int type = (bits >> 30) & 1, cnt = kMaxLeafPrims == 1 ? 1 : (int)((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
+#if RTB_LEAF_PRELOAD
+    if (!X && type == 0) {
+        // all sphere loads of the leaf in flight before the first test (slots past cnt re-read the last sphere)
+        float4 sp4[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) sp4[k] = __ldg(sc.spheres + first + min(k, cnt - 1));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float t;
+            if (k < cnt && sphere_t<X>(r.o, r.d, r.a, r.inv_a, sp4[k], r.tmin, r.closest, t)) {
+                r.closest = t;
+                r.htype = 0;
+                r.hslot = first + k;
+            }
+        }
+        if (COUNT) wc.spheres += cnt;
+        return;
+    }
+#endif
     for (int k = 0; k < cnt; ++k) {
         float t, al, be;
         bool h;
@@ -300,6 +338,11 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
             }
         }
     }
+}
+
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc) {
+    trav_leaf<X, COUNT>(sc, r, wc, r.ref);
 }
 
 __device__ __forceinline__ HitInfo trav_hit(const RayTrav& r) {

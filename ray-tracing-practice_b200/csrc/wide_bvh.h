@@ -10,6 +10,7 @@
 #pragma once
 #include <cstdint>
 #include <vector>
+#include "leaf_size.h"
 
 namespace rtb {
 
@@ -56,6 +57,6 @@ std::vector<PrimBox> make_prim_boxes(const SphereIn* sp, int S, const PlaneIn* p
 int validate_wide_bvh(const WideBvh& bvh, const std::vector<PrimBox>& prims);
 
 // Builds the wide BVH over `prims` (boxes must already be conservative).  max_leaf in [1,4].
-WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf = 4);
+WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf = kMaxLeafPrims);
 
 }  // namespace rtb
