@@ -20,6 +20,9 @@
 #ifndef RTB_LOOP_SHAPE
 #define RTB_LOOP_SHAPE 1
 #endif
+#ifndef RTB_POP_PRELOAD
+#define RTB_POP_PRELOAD 1
+#endif
 #ifndef RTB_LEAF_K
 #define RTB_LEAF_K 12
 #endif
@@ -158,8 +161,12 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         // iteration, together with the lanes that were at inner nodes anyway
         while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
             if (ref_is_leaf(rt.ref)) {
+#if RTB_POP_PRELOAD
+                trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
+#else
                 trav_leaf<X, COUNT>(sc, rt, wc);
                 trav_pop(rt, stk);
+#endif
             }
             if (ref_is_inner(rt.ref)) {
                 if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);

@@ -41,6 +41,9 @@ struct DevScene {
 #ifndef RTB_TOPREG
 #define RTB_TOPREG 0
 #endif
+#ifndef RTB_SORT_PARTIAL
+#define RTB_SORT_PARTIAL 1
+#endif
 #ifndef RTB_LEAF_PRELOAD
 #define RTB_LEAF_PRELOAD 0
 #endif
@@ -264,6 +267,22 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
         int ra_ = s_ ? cr[j] : cr[i], rb_ = s_ ? cr[i] : cr[j];    \
         tn[i] = ta_; tn[j] = tb_; cr[i] = ra_; cr[j] = rb_;        \
     }
+#if RTB_SORT_PARTIAL
+    // three comparators: entry 0 is the nearest child, entry 2 the nearer of the two pair losers' winners; 1 and 3 unordered
+    RTB_CSWAP(0, 1) RTB_CSWAP(2, 3) RTB_CSWAP(0, 2)
+#undef RTB_CSWAP
+    {
+        const int order[3] = {3, 1, 2};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int i = order[k];
+            if (tn[i] < inf) {
+                stk.push(r.sp, tn[i], cr[i]);
+                ++r.sp;
+            }
+        }
+    }
+#else
     RTB_CSWAP(0, 1) RTB_CSWAP(2, 3) RTB_CSWAP(0, 2) RTB_CSWAP(1, 3) RTB_CSWAP(1, 2)
 #undef RTB_CSWAP
     // push far-to-near: entries 3,2,1 ; continue with entry 0
@@ -274,6 +293,7 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
             ++r.sp;
         }
     }
+#endif
 #if RTB_TOPREG
     if (tn[1] < inf) { r.top_t = tn[1]; r.top_r = cr[1]; }
 #endif
@@ -343,6 +363,23 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
 template <bool X, bool COUNT>
 __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc) {
     trav_leaf<X, COUNT>(sc, r, wc, r.ref);
+}
+
+// leaf step followed by the pop, with the top stack entry requested BEFORE the primitive test so that the two loads
+// (primitive, stack entry) are in flight together
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trav_leaf_pop(const DevScene& sc, RayTrav& r, const TravStack& stk, WorkCount& wc) {
+    float t0 = 0.0f;
+    int e0 = kRefDone;
+    const bool have = r.sp > 0;
+    if (have) stk.load(r.sp - 1, t0, e0);
+    trav_leaf<X, COUNT>(sc, r, wc, r.ref);
+    r.ref = kRefDone;
+    if (have) {
+        --r.sp;
+        if (t0 <= r.closest) r.ref = e0;
+        else trav_pop(r, stk);
+    }
 }
 
 __device__ __forceinline__ HitInfo trav_hit(const RayTrav& r) {
