@@ -20,9 +20,6 @@
 #ifndef RTB_LOOP_SHAPE
 #define RTB_LOOP_SHAPE 1
 #endif
-#ifndef RTB_POP_PRELOAD
-#define RTB_POP_PRELOAD 1
-#endif
 #ifndef RTB_LEAF_K
 #define RTB_LEAF_K 12
 #endif
@@ -147,27 +144,12 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         }
         if (__all_sync(full, rt.ref == kRefIdle)) break;  // no pixels left for any lane
         // ================= TRACE phase: every lane runs its segment's closest-hit traversal to completion (traverse.cuh).
-        // Measured on B200: warp votes that batch the leaf tests (lanes wait until k hold a leaf) cost more than they save
-        // once the stack is in local memory -- the plain per-lane loop is 4-8 % faster than any vote threshold.
-#if RTB_LOOP_SHAPE == 0
+        // One iteration = (leaf test + pop)? then (wide node)?: a lane whose leaf test pops a wide node visits it in the same
+        // iteration, together with the lanes that were at wide nodes anyway.  Measured on B200: warp votes
+        // that batch the leaf tests, lanes waiting for each other, and postponed leaves (below) all cost more than they save.
+#if RTB_LOOP_SHAPE == 1
         while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
-            bool pop = true;
-            if (ref_is_leaf(rt.ref)) trav_leaf<X, COUNT>(sc, rt, wc);
-            else pop = trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc);
-            if (pop) trav_pop(rt, stk);
-        }
-#elif RTB_LOOP_SHAPE == 1
-        // one iteration = (leaf + pop)? then (inner node)?: a lane whose leaf test pops an inner node visits it in the same
-        // iteration, together with the lanes that were at inner nodes anyway
-        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
-            if (ref_is_leaf(rt.ref)) {
-#if RTB_POP_PRELOAD
-                trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
-#else
-                trav_leaf<X, COUNT>(sc, rt, wc);
-                trav_pop(rt, stk);
-#endif
-            }
+            if (ref_is_leaf(rt.ref)) trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
             if (ref_is_inner(rt.ref)) {
                 if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
             }
@@ -195,17 +177,6 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     }
                 }
                 if ((ib | mb) == 0u) break;
-            }
-        }
-#else
-        // inner first, then leaf
-        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
-            if (ref_is_inner(rt.ref)) {
-                if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
-            }
-            if (ref_is_leaf(rt.ref)) {
-                trav_leaf<X, COUNT>(sc, rt, wc);
-                trav_pop(rt, stk);
             }
         }
 #endif

@@ -38,14 +38,8 @@ struct DevScene {
 // the first design; measured on B200 it is 10 % SLOWER than all-local (two LDS/STS + address math + a shared/local branch
 // per push and pop, and it takes L1 capacity away from the nodes), so the default is 0.  The builder guarantees
 // max_stack <= 64.
-#ifndef RTB_TOPREG
-#define RTB_TOPREG 0
-#endif
 #ifndef RTB_SORT_PARTIAL
 #define RTB_SORT_PARTIAL 1
-#endif
-#ifndef RTB_LEAF_PRELOAD
-#define RTB_LEAF_PRELOAD 0
 #endif
 constexpr int kSmemStack = RTB_SMEM_STACK;
 constexpr int kLocalStack = 64 - kSmemStack;
@@ -153,10 +147,6 @@ struct RayTrav {
     int ref, sp;
     int htype, hslot, horig;             // closest hit so far: -1 miss / 0 sphere / 1 plane, re-ordered slot, caller's index
     unsigned int best_key;
-#if RTB_TOPREG
-    float top_t;                         // copy of the top stack entry: a pop never waits for its own load
-    int top_r;
-#endif
 };
 
 // per-thread stack: kSmemStack entries in shared memory (strided by the block size), the rest in local memory as
@@ -214,12 +204,7 @@ __device__ __forceinline__ void trav_pop(RayTrav& r, const TravStack& stk) {
         --r.sp;
         float t;
         int e;
-#if RTB_TOPREG
-        t = r.top_t; e = r.top_r;
-        if (r.sp > 0) stk.load(r.sp - 1, r.top_t, r.top_r);
-#else
         stk.load(r.sp, t, e);
-#endif
         if (t <= r.closest) { r.ref = e; break; }
     }
 }
@@ -294,9 +279,6 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
         }
     }
 #endif
-#if RTB_TOPREG
-    if (tn[1] < inf) { r.top_t = tn[1]; r.top_r = cr[1]; }
-#endif
     if (tn[0] < inf) {
         r.ref = cr[0];
         return false;
@@ -309,25 +291,6 @@ template <bool X, bool COUNT>
 __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCount& wc, int leaf_ref) {
     unsigned int bits = (unsigned int)leaf_ref;
     const int type = (bits >> 30) & 1, cnt = kMaxLeafPrims == 1 ? 1 : (int)((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
-#if RTB_LEAF_PRELOAD
-    if (!X && type == 0) {
-        // all sphere loads of the leaf in flight before the first test (slots past cnt re-read the last sphere)
-        float4 sp4[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) sp4[k] = __ldg(sc.spheres + first + min(k, cnt - 1));
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            float t;
-            if (k < cnt && sphere_t<X>(r.o, r.d, r.a, r.inv_a, sp4[k], r.tmin, r.closest, t)) {
-                r.closest = t;
-                r.htype = 0;
-                r.hslot = first + k;
-            }
-        }
-        if (COUNT) wc.spheres += cnt;
-        return;
-    }
-#endif
     for (int k = 0; k < cnt; ++k) {
         float t, al, be;
         bool h;
