@@ -1,0 +1,257 @@
+// lbvh.cuh -- per-element steps of the DEVICE BVH build.
+//
+// Stands where the reference's host builder stands (include/bvh_builder.h:52-120: recursive median split with
+// std::nth_element, ~1.8 s for 1M primitives on one core) and next to this repository's own host builder
+// (wide_bvh.cpp: binned SAH, better trees, tens of ms).  This one runs on the GPU in a few hundred microseconds to a
+// few milliseconds, for callers that rebuild per frame:
+//     1. conservative primitive boxes (the same arithmetic as make_prim_boxes, wide_bvh.cpp) + centroid bounds
+//     2. 63-bit Morton key of the box centre, top bit = "large primitive" class so that the floor quad and the
+//        polyhedra faces do not inflate the boxes of the small-sphere subtrees they happen to lie in
+//     3. radix sort of (key, primitive)
+//     4. binary radix tree over the sorted keys, one thread per inner node (Karras 2012), ties broken by position
+//     5. bottom-up box fit (second arrival at a node computes it)
+//     6. breadth-first collapse to the 128-byte 4-wide nodes the render kernels read (same slot rules as the host
+//        builder: open the child with the largest surface area until 4 slots are used; one primitive per leaf)
+//     7. per-node depth / worst-case stack need, swept level by level from the leaves up
+// Every step is a function of one element, written once here and called from the kernels in bvh_gpu.cu and -- for the
+// CPU test tier -- from tests/emul, which runs them in plain loops and checks the tree with validate_wide_bvh.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ref_layouts.h"
+
+namespace rtb {
+namespace lbvh {
+
+#ifdef __CUDA_ARCH__
+#define LB_ADD(a, b) __fadd_rn(a, b)
+#define LB_SUB(a, b) __fsub_rn(a, b)
+#define LB_MUL(a, b) __fmul_rn(a, b)
+#define LB_DIV(a, b) __fdiv_rn(a, b)
+#else
+// host builds (tests/emul, and the host halves of bvh_gpu.cu) are compiled without FMA contraction
+#define LB_ADD(a, b) ((a) + (b))
+#define LB_SUB(a, b) ((a) - (b))
+#define LB_MUL(a, b) ((a) * (b))
+#define LB_DIV(a, b) ((a) / (b))
+#endif
+#define LB_HD __host__ __device__ inline
+
+struct Box {
+    float lo[3], hi[3];
+};
+
+LB_HD float lb_min(float a, float b) { return a < b ? a : b; }
+LB_HD float lb_max(float a, float b) { return a > b ? a : b; }
+LB_HD float lb_abs(float a) { return a < 0.f ? -a : a; }
+
+// 2*(dx*dy + dy*dz + dz*dx), 0 for inverted boxes: the ordering key of the collapse (Box3::area in wide_bvh.cpp)
+LB_HD float box_area(const Box& b) {
+    float dx = LB_SUB(b.hi[0], b.lo[0]), dy = LB_SUB(b.hi[1], b.lo[1]), dz = LB_SUB(b.hi[2], b.lo[2]);
+    if (dx < 0 || dy < 0 || dz < 0) return 0.f;
+    return LB_MUL(2.f, LB_ADD(LB_ADD(LB_MUL(dx, dy), LB_MUL(dy, dz)), LB_MUL(dz, dx)));
+}
+LB_HD Box box_union(const Box& a, const Box& b) {
+    Box r;
+    for (int k = 0; k < 3; ++k) { r.lo[k] = lb_min(a.lo[k], b.lo[k]); r.hi[k] = lb_max(a.hi[k], b.hi[k]); }
+    return r;
+}
+
+// ---- step 1: conservative boxes.  Bit for bit the boxes of make_prim_boxes (wide_bvh.cpp): supersets of everything the
+// reference's leaf tests (include/sphere.h:24, include/plane.h:57) can accept.  i < S: sphere i, else plane i-S.
+LB_HD Box prim_box(const SphereIn* sp, int S, const PlaneIn* pl, int i) {
+    Box b;
+    if (i < S) {
+        const SphereIn& s = sp[i];
+        float r = lb_abs(s.r);
+        float m = lb_max(lb_abs(s.c[0]), lb_max(lb_abs(s.c[1]), lb_abs(s.c[2])));
+        float pad = LB_ADD(LB_MUL(1e-3f, r), LB_MUL(1e-6f, LB_ADD(m, r)));
+        for (int a = 0; a < 3; ++a) {
+            b.lo[a] = LB_SUB(LB_SUB(s.c[a], r), pad);
+            b.hi[a] = LB_ADD(LB_ADD(s.c[a], r), pad);
+        }
+    } else {
+        const PlaneIn& p = pl[i - S];
+        float m = 0.f;
+        for (int a = 0; a < 3; ++a) {
+            float c0 = p.base[a], c1 = LB_ADD(p.base[a], p.u[a]), c2 = LB_ADD(p.base[a], p.v[a]);
+            float c3 = LB_ADD(LB_ADD(p.base[a], p.u[a]), p.v[a]);
+            float lo = lb_min(c0, lb_min(c1, c2)), hi = lb_max(c0, lb_max(c1, c2));
+            if (p.type != 2) { lo = lb_min(lo, c3); hi = lb_max(hi, c3); }
+            b.lo[a] = lo;
+            b.hi[a] = hi;
+            m = lb_max(m, lb_max(lb_abs(lo), lb_abs(hi)));
+        }
+        float pad = LB_ADD(1e-4f, LB_MUL(4e-6f, m));
+        for (int a = 0; a < 3; ++a) { b.lo[a] = LB_SUB(b.lo[a], pad); b.hi[a] = LB_ADD(b.hi[a], pad); }
+    }
+    return b;
+}
+
+// floats as order-preserving unsigned keys, so scene bounds reduce with integer atomicMin/atomicMax
+LB_HD uint32_t float_to_ordered(float f) {
+    union { float f; uint32_t u; } c;
+    c.f = f;
+    return (c.u & 0x80000000u) ? ~c.u : (c.u | 0x80000000u);
+}
+LB_HD float ordered_to_float(uint32_t u) {
+    union { float f; uint32_t u; } c;
+    c.u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+    return c.f;
+}
+
+// ---- step 2: Morton key
+LB_HD uint64_t spread21(uint32_t v) {  // 21 bits -> every third bit of 63
+    uint64_t x = v & 0x1fffffu;
+    x = (x | (x << 32)) & 0x001f00000000ffffull;
+    x = (x | (x << 16)) & 0x001f0000ff0000ffull;
+    x = (x | (x << 8)) & 0x100f00f00f00f00full;
+    x = (x | (x << 4)) & 0x10c30c30c30c30c3ull;
+    x = (x | (x << 2)) & 0x1249249249249249ull;
+    return x;
+}
+constexpr float kLargeFraction = 1.f / 32.f;  // a primitive wider than this fraction of the scene goes to the "large" class
+
+// cmin / cmax: bounds of the box centres.  key bit 63 = large class, bits 62..0 = Morton code of the centre.
+LB_HD uint64_t morton_key(const Box& b, const float cmin[3], const float cmax[3]) {
+    float ext = lb_max(LB_SUB(cmax[0], cmin[0]), lb_max(LB_SUB(cmax[1], cmin[1]), LB_SUB(cmax[2], cmin[2])));
+    uint32_t q[3];
+    float wide = 0.f;
+    for (int a = 0; a < 3; ++a) {
+        float e = LB_SUB(cmax[a], cmin[a]);
+        float c = LB_MUL(0.5f, LB_ADD(b.lo[a], b.hi[a]));
+        float x = e > 0.f ? LB_MUL(LB_DIV(LB_SUB(c, cmin[a]), e), 2097152.f) : 0.f;
+        x = lb_min(lb_max(x, 0.f), 2097151.f);
+        q[a] = (uint32_t)x;
+        wide = lb_max(wide, LB_SUB(b.hi[a], b.lo[a]));
+    }
+    uint64_t key = (spread21(q[0]) << 2) | (spread21(q[1]) << 1) | spread21(q[2]);
+    if (ext > 0.f && wide > LB_MUL(kLargeFraction, ext)) key |= 1ull << 63;
+    return key;
+}
+
+// ---- step 4: binary radix tree (Karras, "Maximizing parallelism in the construction of BVHs, octrees and k-d trees",
+// HPG 2012).  n sorted keys, inner nodes 0..n-2 (root 0), leaves referenced as (n-1)+position.
+LB_HD int lb_clz64(uint64_t x) {
+#ifdef __CUDA_ARCH__
+    return __clzll((long long)x);
+#else
+    return x ? __builtin_clzll(x) : 64;
+#endif
+}
+LB_HD int lb_clz32(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __clz((int)x);
+#else
+    return x ? __builtin_clz(x) : 32;
+#endif
+}
+LB_HD int key_delta(const uint64_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + lb_clz32((uint32_t)i ^ (uint32_t)j);  // equal keys: the position breaks the tie
+    return lb_clz64(a ^ b);
+}
+// children of inner node i: node ids in [0, 2n-1): inner c -> c, leaf at sorted position p -> (n-1)+p
+LB_HD void radix_node(const uint64_t* keys, int n, int i, int& left, int& right) {
+    int d = key_delta(keys, n, i, i + 1) - key_delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
+    int dmin = key_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (key_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (key_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = key_delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) / 2;
+        if (key_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + (d < 0 ? -1 : 0);
+    int lo = i < j ? i : j, hi = i < j ? j : i;
+    left = (lo == gamma) ? (n - 1) + gamma : gamma;
+    right = (hi == gamma + 1) ? (n - 1) + gamma + 1 : gamma + 1;
+}
+
+// ---- step 6: collapse.  `bin` is the binary inner node that roots this wide node; kids[] receives up to four binary
+// node ids (-1 unused).  Same rule as the host builder: start from the two children, keep opening the inner child with
+// the largest area (first one on ties) until four slots are used.  Returns the number of INNER kids.
+LB_HD int collapse_pick(const int2* children, const Box* boxes, int n, int bin, int kids[4]) {
+    int nk = 0;
+    kids[0] = kids[1] = kids[2] = kids[3] = -1;
+    if (n == 1) {  // single-primitive scene: the root wide node holds the one leaf
+        kids[0] = 0;
+        return 0;
+    }
+    kids[nk++] = children[bin].x;
+    kids[nk++] = children[bin].y;
+    while (nk < 4) {
+        int pick = -1;
+        float pa = -1.f;
+        for (int k = 0; k < nk; ++k) {
+            if (kids[k] >= n - 1) continue;  // leaf
+            float a = box_area(boxes[kids[k]]);
+            if (a > pa) { pa = a; pick = k; }
+        }
+        if (pick < 0) break;
+        int open = kids[pick];
+        kids[pick] = children[open].x;
+        kids[nk++] = children[open].y;
+    }
+    int inner = 0;
+    for (int k = 0; k < nk; ++k) inner += kids[k] < n - 1;
+    return inner;
+}
+
+constexpr int32_t kEmpty = 0x7fffffff;  // == kEmptyChild (wide_bvh.h)
+LB_HD int32_t make_leaf_ref(int type, int first) { return (int32_t)(0x80000000u | ((uint32_t)type << 30) | (uint32_t)first); }
+
+// writes the 32 floats of wide node `out` (layout of WideNode, wide_bvh.h).  next_base + off + rank = index of an inner
+// kid's wide node (next level, breadth-first); next_items[off + rank] = its binary node.  leaf_refs[p] = leaf reference
+// of the primitive at sorted position p.
+LB_HD void collapse_write(const Box* boxes, const int32_t* leaf_refs, int n, const int kids[4], int next_base, int off,
+                          float* out, int* next_items) {
+    const float inf = __builtin_huge_valf();
+    int32_t* child = reinterpret_cast<int32_t*>(out + 24);
+    int rank = 0;
+    for (int i = 0; i < 4; ++i) {
+        int k = kids[i];
+        if (k < 0) {
+            for (int a = 0; a < 3; ++a) { out[a * 4 + i] = inf; out[12 + a * 4 + i] = -inf; }
+            child[i] = kEmpty;
+        } else {
+            const Box& b = boxes[k];
+            for (int a = 0; a < 3; ++a) { out[a * 4 + i] = b.lo[a]; out[12 + a * 4 + i] = b.hi[a]; }
+            if (k >= n - 1) {
+                child[i] = leaf_refs[k - (n - 1)];
+            } else {
+                child[i] = next_base + off + rank;
+                next_items[off + rank] = k;
+                ++rank;
+            }
+        }
+        child[4 + i] = 0;  // pad
+    }
+}
+
+// ---- step 7: depth and worst-case traversal stack need of wide node `w`, from its children's (already final) values
+LB_HD void depth_need(const float* node, const int* dep, const int* need, int& d_out, int& n_out) {
+    const int32_t* child = reinterpret_cast<const int32_t*>(node + 24);
+    int k = 0, dmax = 0, nmax = 0;
+    for (int c = 0; c < 4; ++c) {
+        if (child[c] == kEmpty) continue;
+        ++k;
+        if (child[c] >= 0) {
+            dmax = dep[child[c]] > dmax ? dep[child[c]] : dmax;
+            nmax = need[child[c]] > nmax ? need[child[c]] : nmax;
+        }
+    }
+    d_out = 1 + dmax;
+    n_out = (k > 0 ? k - 1 : 0) + nmax;
+}
+
+}  // namespace lbvh
+}  // namespace rtb
