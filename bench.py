@@ -302,9 +302,33 @@ def main():
             line["reference_cuda"] = reference_cuda_leg(rt, scene, hs, cam, W, H, spp)
         except Exception as e:
             line["reference_cuda"] = {"unavailable": repr(e)}
+        try:
+            line["bvh_build"] = bvh_build_leg(rt, hs, cam, stats)
+        except Exception as e:
+            line["bvh_build"] = {"unavailable": repr(e)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def bvh_build_leg(rt, hs, cam, host_stats):
+    """the device BVH build (rt_scene_create_ex, RT_BVH_GPU_LBVH) next to the host SAH build of the
+    same scene -- build time of each, and what the faster-to-build tree costs at render time (one frame, same kernel)."""
+    best = None
+    for _ in range(3):
+        sc = rt.Scene.from_host(hs, bvh_builder=rt.BVH_GPU_LBVH)
+        st = sc.stats()
+        if best is None or st["build_ms"] < best["build_ms"]:
+            best = st
+        if _ < 2:
+            sc.close()
+    sc.render(cam, seed=0)
+    _, info = sc.render(cam, seed=0)
+    sc.close()
+    return {"host_sah_build_ms": host_stats["build_ms"], "gpu_lbvh_build_ms": best["build_ms"], "gpu_lbvh_input_upload_ms": best["input_upload_ms"],
+            "host_sah_nodes": host_stats["wide_nodes"], "gpu_lbvh_nodes": best["wide_nodes"], "gpu_lbvh_depth": best["wide_depth"],
+            "gpu_lbvh_max_stack": best["max_stack"], "gpu_lbvh_render_mrays_s": info["segments"] / info["kernel_ms"] / 1e3,
+            "gpu_lbvh_render_kernel_ms": info["kernel_ms"]}
 
 
 def reference_cuda_leg(rt, scene, hs, cam, W, H, spp):

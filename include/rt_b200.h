@@ -72,13 +72,30 @@ typedef struct rt_scene_stats {
     int wide_nodes, wide_depth, max_stack, leaves;
     float sah_cost, build_ms, upload_ms;
     unsigned long long device_bytes;
+    int bvh_builder;            /* RT_BVH_* the tree was built with */
+    float input_upload_ms;      /* RT_BVH_GPU_LBVH: allocation + H2D of the caller's arrays (part of upload_ms) */
 } rt_scene_stats;
+
+/* Which builder replaces build_bvh (include/bvh_builder.h:99-120). */
+enum { RT_BVH_HOST_SAH = 0,    /* host, binned SAH, multi-threaded: best trees (default) */
+       RT_BVH_GPU_LBVH = 1 };  /* device: Morton sort + binary radix tree + bottom-up fit + wide collapse, all on the GPU
+                                  (SURVEY 8 f1): ~100x faster to build, ~1.3x more node visits per ray */
+typedef struct rt_scene_opts {
+    int struct_size;            /* = sizeof(rt_scene_opts) */
+    int bvh_builder;            /* RT_BVH_* */
+} rt_scene_opts;
 
 /* Replaces create_scene's upload + build_bvh (src/main.cu:428-478, include/bvh_builder.h:99): copies the three
  * arrays, builds the wide BVH and SoA primitive buffers, uploads.  tex_rgba: tw*th RGBA float texels exactly as
  * stbi_loadf(...,4) returns them (src/main.cu:18), applied to materials[tex_material_idx]; NULL/-1 for none. */
 int rt_scene_create(const void* spheres, int num_spheres, const void* planes, int num_planes, const void* materials,
                     int num_materials, const float* tex_rgba, int tex_w, int tex_h, int tex_material_idx, rt_scene** out);
+/* Same with options (opts may be NULL = rt_scene_create).  With RT_BVH_GPU_LBVH the caller's arrays are uploaded as they
+ * are and the tree + SoA buffers are produced by kernels (csrc/bvh_gpu.cu); results are identical in exact mode (the closest
+ * hit does not depend on the tree), the environment variable RTB_BVH_BUILDER=gpu selects it where opts is NULL. */
+int rt_scene_create_ex(const void* spheres, int num_spheres, const void* planes, int num_planes, const void* materials,
+                       int num_materials, const float* tex_rgba, int tex_w, int tex_h, int tex_material_idx,
+                       const rt_scene_opts* opts, rt_scene** out);
 /* Replaces destroy_scene_arrays + destroy_all_materials (src/main.cu:310-344). */
 void rt_scene_destroy(rt_scene* scene);
 int rt_scene_get_stats(const rt_scene* scene, rt_scene_stats* out);

@@ -35,9 +35,10 @@ QUAD, ELLIPSE, TRIANGLE = 0, 1, 2
 KERNEL_MEGA, KERNEL_WAVEFRONT, KERNEL_POOL = 0, 1, 2
 RNG_PHILOX, RNG_REFERENCE = 0, 1
 TEX_CPU, TEX_GPU = 0, 1
+BVH_HOST_SAH, BVH_GPU_LBVH = 0, 1
 TILE = 16
 
-C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
+C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
                  "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
                  "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_version"]
 
@@ -62,7 +63,12 @@ class WorkCounters(C.Structure):
 class SceneStats(C.Structure):
     _fields_ = [("num_spheres", C.c_int), ("num_planes", C.c_int), ("num_materials", C.c_int), ("wide_nodes", C.c_int),
                 ("wide_depth", C.c_int), ("max_stack", C.c_int), ("leaves", C.c_int), ("sah_cost", C.c_float),
-                ("build_ms", C.c_float), ("upload_ms", C.c_float), ("device_bytes", C.c_ulonglong)]
+                ("build_ms", C.c_float), ("upload_ms", C.c_float), ("device_bytes", C.c_ulonglong),
+                ("bvh_builder", C.c_int), ("input_upload_ms", C.c_float)]
+
+
+class SceneOpts(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("bvh_builder", C.c_int)]
 
 
 def build(force=False):
@@ -85,6 +91,7 @@ def lib():
         L.rt_last_error.restype = C.c_char_p
         L.rt_version.restype = C.c_char_p
         L.rt_scene_create.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp]
+        L.rt_scene_create_ex.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp, vp]
         L.rt_scene_destroy.argtypes = [vp]
         L.rt_scene_get_stats.argtypes = [vp, vp]
         L.rt_render.argtypes = [vp, vp, vp, vp, vp, vp, vp]
@@ -259,7 +266,7 @@ def bvh_check(spheres, planes):
 class Scene:
     """rt_scene handle: the arrays create_scene produces, uploaded as wide BVH + SoA buffers (needs a GPU)."""
 
-    def __init__(self, spheres, planes, materials, tex=None, tex_material=-1):
+    def __init__(self, spheres, planes, materials, tex=None, tex_material=-1, bvh_builder=None):
         self.h = C.c_void_p()
         sp = np.ascontiguousarray(spheres, SPHERE)
         pl = np.ascontiguousarray(planes, PLANE)
@@ -268,13 +275,18 @@ class Scene:
         if tex is not None:
             tex = np.ascontiguousarray(tex, np.float32)
             th, tw = tex.shape[0], tex.shape[1]
-        _check(lib().rt_scene_create(_ptr(sp), len(sp), _ptr(pl), len(pl), _ptr(mt), len(mt), _ptr(tex), tw, th,
-                                     tex_material if tex is not None else -1, C.byref(self.h)))
+        if bvh_builder is None:
+            _check(lib().rt_scene_create(_ptr(sp), len(sp), _ptr(pl), len(pl), _ptr(mt), len(mt), _ptr(tex), tw, th,
+                                         tex_material if tex is not None else -1, C.byref(self.h)))
+        else:
+            so = SceneOpts(C.sizeof(SceneOpts), int(bvh_builder))
+            _check(lib().rt_scene_create_ex(_ptr(sp), len(sp), _ptr(pl), len(pl), _ptr(mt), len(mt), _ptr(tex), tw, th,
+                                            tex_material if tex is not None else -1, C.byref(so), C.byref(self.h)))
 
     @classmethod
-    def from_host(cls, host):
+    def from_host(cls, host, bvh_builder=None):
         sp, pl, mt, tex = host.arrays()
-        return cls(sp, pl, mt, tex, 0)
+        return cls(sp, pl, mt, tex, 0, bvh_builder=bvh_builder)
 
     def stats(self):
         s = SceneStats()

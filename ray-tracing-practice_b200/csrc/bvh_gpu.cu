@@ -1,0 +1,349 @@
+// bvh_gpu.cu -- device BVH build + scene packing: the kernels around the per-element steps
+// of lbvh.cuh.  Replaces build_bvh + the array uploads of create_scene (include/bvh_builder.h:99-120,
+// src/main.cu:428-474) for callers that rebuild often: the caller's AoS arrays go up once and everything the render
+// kernels read -- 128-byte wide nodes, leaf-ordered SoA spheres / planes -- is produced on the GPU.
+// The only library call is cub's radix sort / prefix sum (CUDA toolkit); the tree construction is hand-written.
+#include "bvh_gpu.h"
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <chrono>
+#include <cstdlib>
+#include <vector>
+
+#include "lbvh.cuh"
+
+namespace rtb {
+namespace {
+
+using lbvh::Box;
+constexpr int kThreads = 256;
+inline int blocks_for(int n) { return (n + kThreads - 1) / kThreads; }
+
+// ---- 1. boxes + bounds of the box centres (ordered-uint atomics; bounds6 = min xyz, max xyz)
+__global__ void k_boxes(const SphereIn* __restrict__ sp, int S, const PlaneIn* __restrict__ pl, int n, Box* __restrict__ prim_boxes,
+                        unsigned int* __restrict__ bounds6) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
+    if (i < n) {
+        Box b = lbvh::prim_box(sp, S, pl, i);
+        prim_boxes[i] = b;
+        for (int a = 0; a < 3; ++a) {
+            unsigned int c = lbvh::float_to_ordered(__fmul_rn(0.5f, __fadd_rn(b.lo[a], b.hi[a])));
+            mn[a] = c;
+            mx[a] = c;
+        }
+    }
+    for (int a = 0; a < 3; ++a) {
+        mn[a] = __reduce_min_sync(0xffffffffu, mn[a]);
+        mx[a] = __reduce_max_sync(0xffffffffu, mx[a]);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        for (int a = 0; a < 3; ++a) {
+            atomicMin(&bounds6[a], mn[a]);
+            atomicMax(&bounds6[3 + a], mx[a]);
+        }
+    }
+}
+
+// ---- 2. Morton keys
+__global__ void k_keys(const Box* __restrict__ prim_boxes, int n, const unsigned int* __restrict__ bounds6,
+                       unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float cmin[3], cmax[3];
+    for (int a = 0; a < 3; ++a) {
+        cmin[a] = lbvh::ordered_to_float(bounds6[a]);
+        cmax[a] = lbvh::ordered_to_float(bounds6[3 + a]);
+    }
+    keys[i] = lbvh::morton_key(prim_boxes[i], cmin, cmax);
+    vals[i] = (unsigned int)i;
+}
+
+// ---- 3b. after the sort: 1 where the primitive at sorted position p is a sphere (scanned into sphere positions)
+__global__ void k_flags(const unsigned int* __restrict__ vals, int n, int S, int* __restrict__ is_sphere) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) is_sphere[p] = vals[p] < (unsigned int)S;
+}
+
+// ---- 3c. leaf boxes, leaf references and the leaf-ordered SoA primitive streams (layouts of scene_pack.h)
+__global__ void k_pack(const SphereIn* __restrict__ sp, int S, const PlaneIn* __restrict__ pl, const unsigned int* __restrict__ vals,
+                       const int* __restrict__ sphere_pos, const Box* __restrict__ prim_boxes, int n, Box* __restrict__ boxes,
+                       int* __restrict__ leaf_refs, float4* __restrict__ spheres, int2* __restrict__ sphere_meta,
+                       float4* __restrict__ planes) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    int id = (int)vals[p];
+    boxes[(n - 1) + p] = prim_boxes[id];
+    if (id < S) {
+        int pos = sphere_pos[p];
+        const SphereIn& s = sp[id];
+        spheres[pos] = make_float4(s.c[0], s.c[1], s.c[2], s.r);
+        sphere_meta[pos] = make_int2(s.mat, id);
+        leaf_refs[p] = lbvh::make_leaf_ref(0, pos);
+    } else {
+        int pos = p - sphere_pos[p];
+        const PlaneIn& q = pl[id - S];
+        float4* o = planes + 5 * (size_t)pos;
+        o[0] = make_float4(q.n[0], q.n[1], q.n[2], q.D);
+        o[1] = make_float4(q.w[0], q.w[1], q.w[2], __int_as_float(q.type));
+        o[2] = make_float4(q.u[0], q.u[1], q.u[2], __int_as_float(q.mat));
+        o[3] = make_float4(q.v[0], q.v[1], q.v[2], __int_as_float(id - S));
+        o[4] = make_float4(q.base[0], q.base[1], q.base[2], 0.f);
+        leaf_refs[p] = lbvh::make_leaf_ref(1, pos);
+    }
+}
+
+// ---- 4. binary radix tree
+__global__ void k_radix(const unsigned long long* __restrict__ keys, int n, int2* __restrict__ children, int* __restrict__ parent) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int l, r;
+    lbvh::radix_node((const uint64_t*)keys, n, i, l, r);
+    children[i] = make_int2(l, r);
+    parent[l] = i;
+    parent[r] = i;
+}
+
+// ---- 5. bottom-up fit: the second thread to arrive at an inner node owns it
+__global__ void k_fit(const int2* __restrict__ children, const int* __restrict__ parent, int n, Box* boxes, unsigned int* arrived) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n || n < 2) return;
+    int cur = parent[(n - 1) + p];
+    while (true) {
+        __threadfence();
+        if (atomicAdd(&arrived[cur], 1u) == 0u) return;
+        int2 ch = children[cur];
+        // the children were written by other threads of this launch: read them from L2, not from this SM's L1
+        const float* a = reinterpret_cast<const float*>(boxes + ch.x);
+        const float* b = reinterpret_cast<const float*>(boxes + ch.y);
+        Box u;
+        for (int k = 0; k < 3; ++k) {
+            u.lo[k] = fminf(__ldcg(a + k), __ldcg(b + k));
+            u.hi[k] = fmaxf(__ldcg(a + 3 + k), __ldcg(b + 3 + k));
+        }
+        boxes[cur] = u;
+        if (cur == 0) return;
+        cur = parent[cur];
+    }
+}
+
+// ---- 6. collapse, one breadth-first level per launch pair
+__global__ void k_collapse_count(const int2* __restrict__ children, const Box* __restrict__ boxes, int n,
+                                 const int* __restrict__ items, int count, int4* __restrict__ kids_out, int* __restrict__ inner_cnt) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    int kids[4];
+    inner_cnt[k] = lbvh::collapse_pick(children, boxes, n, items[k], kids);
+    kids_out[k] = make_int4(kids[0], kids[1], kids[2], kids[3]);
+}
+__global__ void k_collapse_write(const Box* __restrict__ boxes, const int* __restrict__ leaf_refs, int n,
+                                 const int* __restrict__ items, const int4* __restrict__ kids_in,
+                                 const int* __restrict__ inner_off, const int* __restrict__ inner_cnt, int count, int level_base,
+                                 float* __restrict__ nodes, int* __restrict__ next_items, int* __restrict__ next_count,
+                                 float prim_cost, double* __restrict__ sah) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    float cost = 0.f;
+    if (k < count) {
+        int4 kd = kids_in[k];
+        int kids[4] = {kd.x, kd.y, kd.z, kd.w};
+        lbvh::collapse_write(boxes, leaf_refs, n, kids, level_base + count, inner_off[k], nodes + 32 * (size_t)(level_base + k), next_items);
+        if (k == count - 1) *next_count = inner_off[k] + inner_cnt[k];
+        float root_area = fmaxf(lbvh::box_area(boxes[0]), 1e-30f);
+        cost = lbvh::box_area(boxes[n == 1 ? 0 : items[k]]) / root_area;
+        for (int c = 0; c < 4; ++c)
+            if (kids[c] >= n - 1) cost += prim_cost * lbvh::box_area(boxes[kids[c]]) / root_area;
+    }
+    for (int o = 16; o > 0; o >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, o);
+    if ((threadIdx.x & 31) == 0 && cost != 0.f) atomicAdd(sah, (double)cost);
+}
+
+// ---- 7. depth / stack need of one level (children live in later levels, already final)
+__global__ void k_depth(const float* __restrict__ nodes, int base, int count, int* dep, int* need) {
+    int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    int d, s;
+    lbvh::depth_need(nodes + 32 * (size_t)(base + k), dep, need, d, s);
+    dep[base + k] = d;
+    need[base + k] = s;
+}
+
+struct Arena {
+    char* base = nullptr;
+    size_t size = 0, used = 0;
+    template <class T> T* take(size_t count) {
+        size_t bytes = (count * sizeof(T) + 255) & ~(size_t)255;
+        T* p = reinterpret_cast<T*>(base + used);
+        used += bytes;
+        return p;
+    }
+};
+inline size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
+
+}  // namespace
+
+#define BG_CUDA(expr)                     \
+    do {                                  \
+        cudaError_t e_ = (expr);          \
+        if (e_ != cudaSuccess) {          \
+            r.fail_line = __LINE__;       \
+            if (arena.base) cudaFree(arena.base); \
+            if (d_sp) cudaFree(d_sp);     \
+            if (d_pl) cudaFree(d_pl);     \
+            gpu_build_free(r);            \
+            return e_;                    \
+        }                                 \
+    } while (0)
+
+void gpu_build_free(GpuBuildResult& r) {
+    void* bufs[] = {r.d_nodes, r.d_spheres, r.d_sphere_meta, r.d_planes};
+    for (void* b : bufs)
+        if (b) cudaFree(b);
+    r.d_nodes = r.d_spheres = r.d_sphere_meta = r.d_planes = nullptr;
+}
+
+cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, int P, cudaStream_t stream, GpuBuildResult& r) {
+    r = GpuBuildResult{};
+    const int n = S + P;
+    Arena arena;
+    SphereIn* d_sp = nullptr;
+    PlaneIn* d_pl = nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+
+    // outputs (owned by the caller afterwards).  A wide node is rooted at a distinct binary inner node: <= max(n-1,1) nodes.
+    const int max_nodes = n > 1 ? n - 1 : 1;
+    BG_CUDA(cudaMalloc(&r.d_nodes, (size_t)max_nodes * 128));
+    BG_CUDA(cudaMalloc(&r.d_spheres, S ? (size_t)S * 16 : 16));
+    BG_CUDA(cudaMalloc(&r.d_sphere_meta, S ? (size_t)S * 8 : 16));
+    BG_CUDA(cudaMalloc(&r.d_planes, P ? (size_t)P * 80 : 16));
+    r.bytes_nodes = (size_t)max_nodes * 128;
+    r.bytes_prims = (size_t)(S ? S * 24 : 32) + (size_t)(P ? P * 80 : 16);
+
+    if (n == 0) {  // empty scene: one node whose four slots fail every slab test
+        float h[32];
+        for (int a = 0; a < 3; ++a)
+            for (int i = 0; i < 4; ++i) { h[a * 4 + i] = __builtin_huge_valf(); h[12 + a * 4 + i] = -__builtin_huge_valf(); }
+        int32_t* ch = reinterpret_cast<int32_t*>(h + 24);
+        for (int i = 0; i < 4; ++i) { ch[i] = lbvh::kEmpty; ch[4 + i] = 0; }
+        BG_CUDA(cudaMemcpyAsync(r.d_nodes, h, 128, cudaMemcpyHostToDevice, stream));
+        BG_CUDA(cudaStreamSynchronize(stream));
+        r.num_nodes = 1;
+        r.depth = 1;
+        return cudaSuccess;
+    }
+
+    // the caller's arrays, as they are
+    if (S) {
+        BG_CUDA(cudaMalloc((void**)&d_sp, (size_t)S * sizeof(SphereIn)));
+        BG_CUDA(cudaMemcpyAsync(d_sp, h_sp, (size_t)S * sizeof(SphereIn), cudaMemcpyHostToDevice, stream));
+    }
+    if (P) {
+        BG_CUDA(cudaMalloc((void**)&d_pl, (size_t)P * sizeof(PlaneIn)));
+        BG_CUDA(cudaMemcpyAsync(d_pl, h_pl, (size_t)P * sizeof(PlaneIn), cudaMemcpyHostToDevice, stream));
+    }
+
+    // one arena for every temporary
+    size_t sort_tmp = 0, scan_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (unsigned long long*)nullptr, (unsigned long long*)nullptr, (unsigned int*)nullptr,
+                                    (unsigned int*)nullptr, n, 0, 64, stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_tmp, (int*)nullptr, (int*)nullptr, n, stream);
+    size_t need = pad256((size_t)n * sizeof(Box)) + 2 * pad256((size_t)n * 8) + 2 * pad256((size_t)n * 4) +  // prim boxes, keys x2, vals x2
+                  pad256((size_t)(2 * n) * sizeof(Box)) + pad256((size_t)n * 8) + pad256((size_t)(2 * n) * 4) +  // boxes, children, parent
+                  8 * pad256((size_t)n * 4) +       // arrived, is_sphere, sphere_pos, leaf_refs, items x2, inner_cnt, inner_off
+                  pad256((size_t)n * 16) +          // kids
+                  2 * pad256((size_t)max_nodes * 4) +  // dep, need
+                  pad256(sort_tmp) + pad256(scan_tmp) + 4 * 256;
+    BG_CUDA(cudaMalloc((void**)&arena.base, need));
+    arena.size = need;
+    Box* prim_boxes = arena.take<Box>(n);
+    unsigned long long* keys_a = arena.take<unsigned long long>(n);
+    unsigned long long* keys_b = arena.take<unsigned long long>(n);
+    unsigned int* vals_a = arena.take<unsigned int>(n);
+    unsigned int* vals_b = arena.take<unsigned int>(n);
+    Box* boxes = arena.take<Box>(2 * (size_t)n);
+    int2* children = arena.take<int2>(n);
+    int* parent = arena.take<int>(2 * (size_t)n);
+    unsigned int* arrived = arena.take<unsigned int>(n);
+    int* is_sphere = arena.take<int>(n);
+    int* sphere_pos = arena.take<int>(n);
+    int* leaf_refs = arena.take<int>(n);
+    int* items_a = arena.take<int>(n);
+    int* items_b = arena.take<int>(n);
+    int* inner_cnt = arena.take<int>(n);
+    int* inner_off = arena.take<int>(n);
+    int4* kids = arena.take<int4>(n);
+    int* dep = arena.take<int>(max_nodes);
+    int* need_s = arena.take<int>(max_nodes);
+    void* d_sort_tmp = arena.take<char>(sort_tmp);
+    void* d_scan_tmp = arena.take<char>(scan_tmp);
+    unsigned int* bounds6 = arena.take<unsigned int>(8);
+    int* next_count = arena.take<int>(1);
+    double* sah = arena.take<double>(1);
+
+    BG_CUDA(cudaStreamSynchronize(stream));
+    auto t1 = std::chrono::steady_clock::now();
+
+    const unsigned int b6[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    BG_CUDA(cudaMemcpyAsync(bounds6, b6, sizeof b6, cudaMemcpyHostToDevice, stream));
+    BG_CUDA(cudaMemsetAsync(arrived, 0, (size_t)n * 4, stream));
+    BG_CUDA(cudaMemsetAsync(sah, 0, 8, stream));
+    k_boxes<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, n, prim_boxes, bounds6);
+    k_keys<<<blocks_for(n), kThreads, 0, stream>>>(prim_boxes, n, bounds6, keys_a, vals_a);
+    BG_CUDA(cub::DeviceRadixSort::SortPairs(d_sort_tmp, sort_tmp, keys_a, keys_b, vals_a, vals_b, n, 0, 64, stream));
+    k_flags<<<blocks_for(n), kThreads, 0, stream>>>(vals_b, n, S, is_sphere);
+    BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, is_sphere, sphere_pos, n, stream));
+    k_pack<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, vals_b, sphere_pos, prim_boxes, n, boxes, leaf_refs,
+                                                  (float4*)r.d_spheres, (int2*)r.d_sphere_meta, (float4*)r.d_planes);
+    if (n > 1) {
+        k_radix<<<blocks_for(n - 1), kThreads, 0, stream>>>(keys_b, n, children, parent);
+        k_fit<<<blocks_for(n), kThreads, 0, stream>>>(children, parent, n, boxes, arrived);
+    }
+    BG_CUDA(cudaGetLastError());
+
+    // breadth-first collapse; the host only learns each level's size (4 bytes per level)
+    const char* pc = getenv("RTB_COST_PRIM");
+    const float prim_cost = pc ? (float)atof(pc) : 0.5f;
+    std::vector<int> level_base, level_count;
+    int root_item = 0;
+    BG_CUDA(cudaMemcpyAsync(items_a, &root_item, 4, cudaMemcpyHostToDevice, stream));
+    int* cur = items_a;
+    int* nxt = items_b;
+    int base = 0, count = 1;
+    while (count > 0) {
+        if (base + count > max_nodes) { r.fail_line = __LINE__; BG_CUDA(cudaErrorUnknown); }
+        level_base.push_back(base);
+        level_count.push_back(count);
+        k_collapse_count<<<blocks_for(count), kThreads, 0, stream>>>(children, boxes, n, cur, count, kids, inner_cnt);
+        BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, inner_cnt, inner_off, count, stream));
+        k_collapse_write<<<blocks_for(count), kThreads, 0, stream>>>(boxes, leaf_refs, n, cur, kids, inner_off, inner_cnt, count, base,
+                                                                    (float*)r.d_nodes, nxt, next_count, prim_cost, sah);
+        int h_next = 0;
+        BG_CUDA(cudaMemcpyAsync(&h_next, next_count, 4, cudaMemcpyDeviceToHost, stream));
+        BG_CUDA(cudaStreamSynchronize(stream));
+        base += count;
+        count = h_next;
+        int* t = cur; cur = nxt; nxt = t;
+    }
+    r.num_nodes = base;
+    r.levels = (int)level_base.size();
+    for (int l = r.levels - 1; l >= 0; --l)
+        k_depth<<<blocks_for(level_count[l]), kThreads, 0, stream>>>((const float*)r.d_nodes, level_base[l], level_count[l], dep, need_s);
+    double h_sah = 0;
+    BG_CUDA(cudaMemcpyAsync(&r.depth, dep, 4, cudaMemcpyDeviceToHost, stream));
+    BG_CUDA(cudaMemcpyAsync(&r.max_stack, need_s, 4, cudaMemcpyDeviceToHost, stream));
+    BG_CUDA(cudaMemcpyAsync(&h_sah, sah, 8, cudaMemcpyDeviceToHost, stream));
+    BG_CUDA(cudaStreamSynchronize(stream));
+    BG_CUDA(cudaGetLastError());
+    auto t2 = std::chrono::steady_clock::now();
+    r.sah_cost = (float)h_sah;
+    r.leaves = n;
+    r.upload_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    r.build_ms = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    cudaFree(arena.base);
+    if (d_sp) cudaFree(d_sp);
+    if (d_pl) cudaFree(d_pl);
+    return cudaSuccess;
+}
+
+}  // namespace rtb

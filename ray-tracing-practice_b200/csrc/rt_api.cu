@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../include/rt_b200.h"
+#include "bvh_gpu.h"
 #include "kernels.h"
 #include "scene_pack.h"
 #include "wide_bvh.h"
@@ -104,7 +105,16 @@ static int upload(void** dst, const void* src, size_t bytes, unsigned long long&
 
 int rt_scene_create(const void* spheres, int S, const void* planes, int P, const void* materials, int M, const float* tex_rgba,
                     int tw, int th, int tex_mat, rt_scene** out) {
+    return rt_scene_create_ex(spheres, S, planes, P, materials, M, tex_rgba, tw, th, tex_mat, nullptr, out);
+}
+
+int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, const void* materials, int M, const float* tex_rgba,
+                       int tw, int th, int tex_mat, const rt_scene_opts* sopts, rt_scene** out) {
     if (!out) return fail(RT_ERR_INVALID, "rt_scene_create: out is NULL");
+    int builder = RT_BVH_HOST_SAH;
+    if (const char* e = getenv("RTB_BVH_BUILDER")) builder = (!strcmp(e, "gpu") || !strcmp(e, "1")) ? RT_BVH_GPU_LBVH : RT_BVH_HOST_SAH;
+    if (sopts && sopts->struct_size >= (int)(2 * sizeof(int))) builder = sopts->bvh_builder;
+    if (builder != RT_BVH_HOST_SAH && builder != RT_BVH_GPU_LBVH) return fail(RT_ERR_INVALID, "rt_scene_create_ex: unknown bvh_builder");
     *out = nullptr;
     if (S < 0 || P < 0 || M <= 0) return fail(RT_ERR_INVALID, "rt_scene_create: negative primitive count or no materials");
     if ((S && !spheres) || (P && !planes) || !materials) return fail(RT_ERR_INVALID, "rt_scene_create: NULL array");
@@ -125,24 +135,50 @@ int rt_scene_create(const void* spheres, int S, const void* planes, int P, const
     int rc = check_device();
     if (rc) return rc;
 
-    // ---- wide BVH over conservative boxes + SoA primitive buffers in leaf order (host, scene_pack.cpp)
     auto t1 = std::chrono::steady_clock::now();
-    PackedScene pk = pack_scene(sp, S, pl, P, mt, M);
-    const WideBvh& bvh = pk.bvh;
-    if (bvh.max_stack > kSmemStack + kLocalStack)
-        return fail(RT_ERR_UNSUPPORTED, "rt_scene_create: BVH needs a deeper traversal stack than the kernels provide");
-
     rt_scene* s = new rt_scene();
     auto bail = [&](int code) { rt_scene_destroy(s); return code; };
     cudaGetDevice(&s->device);
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, s->device) == cudaSuccess) s->num_sms = prop.multiProcessorCount;
     unsigned long long total = 0;
-    if ((rc = upload(&s->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(WideNode), total))) return bail(rc);
-    if ((rc = upload(&s->d_spheres, pk.spheres.data(), pk.spheres.size() * sizeof(float), total))) return bail(rc);
-    if ((rc = upload(&s->d_sphere_meta, pk.sphere_meta.data(), pk.sphere_meta.size() * sizeof(int), total))) return bail(rc);
-    if ((rc = upload(&s->d_planes, pk.planes.data(), pk.planes.size() * sizeof(float), total))) return bail(rc);
-    if ((rc = upload(&s->d_mats, pk.mats.data(), pk.mats.size() * sizeof(float), total))) return bail(rc);
+    struct { int nodes, depth, max_stack, leaves; float sah, build_ms; } tree{};
+    float gpu_upload_ms = 0.f;
+    if (builder == RT_BVH_GPU_LBVH) {
+        // ---- device build (bvh_gpu.cu): the caller's arrays go up as they are; nodes + SoA streams are produced on the GPU
+        GpuBuildResult g;
+        cudaError_t ge = gpu_build_scene(sp, S, pl, P, nullptr, g);
+        if (ge != cudaSuccess) {
+            cudaGetLastError();
+            char b[256];
+            snprintf(b, sizeof b, "CUDA error = %u (%s) in the device BVH build (bvh_gpu.cu:%d)", (unsigned)ge, cudaGetErrorString(ge), g.fail_line);
+            fail(RT_ERR_CUDA, b);
+            return bail(RT_ERR_CUDA);
+        }
+        s->d_nodes = g.d_nodes;
+        s->d_spheres = g.d_spheres;
+        s->d_sphere_meta = g.d_sphere_meta;
+        s->d_planes = g.d_planes;
+        total += g.bytes_nodes + g.bytes_prims;
+        tree = {g.num_nodes, g.depth, g.max_stack, g.leaves, g.sah_cost, g.build_ms};
+        gpu_upload_ms = g.upload_ms;
+        PackedScene tmp = pack_scene(nullptr, 0, nullptr, 0, mt, M);  // material records only
+        if ((rc = upload(&s->d_mats, tmp.mats.data(), tmp.mats.size() * sizeof(float), total))) return bail(rc);
+    } else {
+        // ---- wide BVH over conservative boxes + SoA primitive buffers in leaf order (host, scene_pack.cpp)
+        PackedScene pk = pack_scene(sp, S, pl, P, mt, M);
+        const WideBvh& bvh = pk.bvh;
+        tree = {(int)bvh.nodes.size(), bvh.depth, bvh.max_stack, bvh.leaves, bvh.sah_cost, pk.build_ms};
+        if ((rc = upload(&s->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(WideNode), total))) return bail(rc);
+        if ((rc = upload(&s->d_spheres, pk.spheres.data(), pk.spheres.size() * sizeof(float), total))) return bail(rc);
+        if ((rc = upload(&s->d_sphere_meta, pk.sphere_meta.data(), pk.sphere_meta.size() * sizeof(int), total))) return bail(rc);
+        if ((rc = upload(&s->d_planes, pk.planes.data(), pk.planes.size() * sizeof(float), total))) return bail(rc);
+        if ((rc = upload(&s->d_mats, pk.mats.data(), pk.mats.size() * sizeof(float), total))) return bail(rc);
+    }
+    if (tree.max_stack > kSmemStack + kLocalStack) {
+        fail(RT_ERR_UNSUPPORTED, "rt_scene_create: BVH needs a deeper traversal stack than the kernels provide");
+        return bail(RT_ERR_UNSUPPORTED);
+    }
     s->dev.tex_mat = -1;
     if (tex_rgba) {
         size_t bytes = (size_t)tw * th * 4 * sizeof(float);
@@ -189,20 +225,23 @@ int rt_scene_create(const void* spheres, int S, const void* planes, int P, const
     s->dev.mats = (const float4*)s->d_mats;
     s->dev.tex = (const float4*)s->d_tex;
     s->dev.tex_obj = s->tex_obj;
-    s->dev.num_nodes = (int)bvh.nodes.size();
+    s->dev.num_nodes = tree.nodes;
     s->default_top = s->dev.num_nodes < 64 ? s->dev.num_nodes : 64;
     s->dev.top_nodes = s->default_top;
 
     s->stats.num_spheres = S;
     s->stats.num_planes = P;
     s->stats.num_materials = M;
-    s->stats.wide_nodes = (int)bvh.nodes.size();
-    s->stats.wide_depth = bvh.depth;
-    s->stats.max_stack = bvh.max_stack;
-    s->stats.leaves = bvh.leaves;
-    s->stats.sah_cost = bvh.sah_cost;
-    s->stats.build_ms = pk.build_ms;
-    s->stats.upload_ms = std::chrono::duration<float, std::milli>(t2 - t1).count();
+    s->stats.wide_nodes = tree.nodes;
+    s->stats.wide_depth = tree.depth;
+    s->stats.max_stack = tree.max_stack;
+    s->stats.leaves = tree.leaves;
+    s->stats.sah_cost = tree.sah;
+    s->stats.build_ms = tree.build_ms;
+    // everything of scene creation that is not the tree build: allocations, H2D of arrays / texture, stream + events
+    s->stats.upload_ms = std::chrono::duration<float, std::milli>(t2 - t1).count() - tree.build_ms;
+    s->stats.bvh_builder = builder;
+    s->stats.input_upload_ms = gpu_upload_ms;
     s->stats.device_bytes = total;
     *out = s;
     return RT_OK;

@@ -1,7 +1,8 @@
 // rt_main.cpp -- drop-in for the reference executable (src/main.cu:572-606): `rt_main [--gpu|--default] < config`.
 // `--cpu` is refused: this build has no CPU render path (the reference's --cpu lives on as oracle/_ref).
 // Extensions (all optional, after the mode): --png | --ppm choose the saver the reference ships but never wires up;
-// --spheres N [--seed S] appends the seeded N-sphere field of BASELINE.json's configs 2-4.
+// --spheres N [--seed S] appends the seeded N-sphere field of BASELINE.json's configs 2-4; --bvh-gpu builds the BVH on
+// the device instead of on the host.
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -22,6 +23,7 @@ int main(int argc, char** argv) {
         else if (a == "--png") format = 1;
         else if (a == "--ppm") format = 2;
         else if (a == "--spheres" && i + 1 < argc) spheres = std::atoi(argv[++i]);
+        else if (a == "--bvh-gpu") setenv("RTB_BVH_BUILDER", "gpu", 1);  // device BVH build (rt_scene_create_ex, RT_BVH_GPU_LBVH)
         else if (a == "--seed" && i + 1 < argc) seed = (unsigned)std::strtoul(argv[++i], nullptr, 10);
     }
     if (want_default) { std::cout << default_config_text(); return 0; }

@@ -61,6 +61,8 @@ def emul():
     E = C.CDLL(so)
     vp, ci, cf = C.c_void_p, C.c_int, C.c_float
     E.emu_scene_create.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp]
+    E.emu_scene_create2.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, ci, vp]
+    E.emu_lbvh_check.argtypes = [vp, ci, vp, ci, vp]
     E.emu_scene_destroy.argtypes = [vp]
     E.emu_trace.argtypes = [vp, vp, ci, cf, cf, ci, vp, vp, vp]
     E.emu_render.argtypes = [vp, vp, ci, ci, ci, C.c_ulonglong, vp, vp]
@@ -69,7 +71,7 @@ def emul():
 
 
 class EmuScene:
-    def __init__(self, E, sp, pl, mt, tex=None, tex_mat=-1):
+    def __init__(self, E, sp, pl, mt, tex=None, tex_mat=-1, builder=0):
         import ctypes as C
         self.E = E
         self.h = C.c_void_p()
@@ -80,8 +82,8 @@ class EmuScene:
             tex = np.ascontiguousarray(tex, np.float32)
             th, tw = tex.shape[:2]
             tp = tex.ctypes.data
-        E.emu_scene_create(self.keep[0].ctypes.data, len(sp), self.keep[1].ctypes.data, len(pl), self.keep[2].ctypes.data,
-                           len(mt), tp, tw, th, tex_mat, C.byref(self.h))
+        E.emu_scene_create2(self.keep[0].ctypes.data, len(sp), self.keep[1].ctypes.data, len(pl), self.keep[2].ctypes.data,
+                            len(mt), tp, tw, th, tex_mat, builder, C.byref(self.h))
 
     def trace(self, rays, exact=1, tmin=0.001, tmax=1e30):
         rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)

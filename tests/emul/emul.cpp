@@ -4,7 +4,10 @@
 // clang-format off
 #include "../../ray-tracing-practice_b200/csrc/path.cuh"
 #include "../../ray-tracing-practice_b200/csrc/scene_pack.h"
+#include "../../ray-tracing-practice_b200/csrc/lbvh.cuh"
 // clang-format on
+#include <algorithm>
+#include <numeric>
 #include <atomic>
 #include <thread>
 #include <vector>
@@ -17,12 +20,153 @@ struct EmuScene {
     DevScene dev{};
 };
 
+// The device BVH build (csrc/bvh_gpu.cu) restated as plain loops over the SAME per-element functions (csrc/lbvh.cuh):
+// one loop per kernel, a stable sort where the device uses cub's radix sort.  Replaces pk's tree and primitive streams.
+static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P, PackedScene& pk) {
+    using lbvh::Box;
+    const int n = S + P;
+    WideBvh& out = pk.bvh;
+    out = WideBvh{};
+    pk.spheres.assign((size_t)S * 4, 0.f);
+    pk.sphere_meta.assign((size_t)S * 2, 0);
+    pk.planes.assign((size_t)P * 20, 0.f);
+    if (n == 0) {
+        WideNode root;
+        for (int a = 0; a < 3; ++a)
+            for (int i = 0; i < 4; ++i) { root.lo[a][i] = __builtin_huge_valf(); root.hi[a][i] = -__builtin_huge_valf(); }
+        for (int i = 0; i < 4; ++i) { root.child[i] = kEmptyChild; root.pad[i] = 0; }
+        out.nodes.push_back(root);
+        out.depth = 1;
+        return;
+    }
+    std::vector<Box> prim_boxes(n);
+    float cmin[3] = {__builtin_huge_valf(), __builtin_huge_valf(), __builtin_huge_valf()}, cmax[3] = {-cmin[0], -cmin[0], -cmin[0]};
+    for (int i = 0; i < n; ++i) {  // k_boxes
+        prim_boxes[i] = lbvh::prim_box(sp, S, pl, i);
+        for (int a = 0; a < 3; ++a) {
+            float c = 0.5f * (prim_boxes[i].lo[a] + prim_boxes[i].hi[a]);
+            // through the same ordered-uint encoding the device reduces with
+            float cc = lbvh::ordered_to_float(lbvh::float_to_ordered(c));
+            cmin[a] = std::min(cmin[a], cc);
+            cmax[a] = std::max(cmax[a], cc);
+        }
+    }
+    std::vector<uint64_t> keys(n);
+    std::vector<unsigned> vals(n);
+    for (int i = 0; i < n; ++i) { keys[i] = lbvh::morton_key(prim_boxes[i], cmin, cmax); vals[i] = (unsigned)i; }  // k_keys
+    std::stable_sort(vals.begin(), vals.end(), [&](unsigned a, unsigned b) { return keys[a] < keys[b]; });
+    std::vector<uint64_t> skeys(n);
+    for (int p = 0; p < n; ++p) skeys[p] = keys[vals[p]];
+    std::vector<int> sphere_pos(n);
+    for (int p = 0, acc = 0; p < n; ++p) { sphere_pos[p] = acc; acc += vals[p] < (unsigned)S; }  // k_flags + scan
+    std::vector<Box> boxes(2 * (size_t)n);
+    std::vector<int> leaf_refs(n);
+    auto i2f = [](int v) { float f; memcpy(&f, &v, 4); return f; };
+    for (int p = 0; p < n; ++p) {  // k_pack
+        int id = (int)vals[p];
+        boxes[(n - 1) + p] = prim_boxes[id];
+        if (id < S) {
+            int pos = sphere_pos[p];
+            float* o = &pk.spheres[4 * (size_t)pos];
+            o[0] = sp[id].c[0]; o[1] = sp[id].c[1]; o[2] = sp[id].c[2]; o[3] = sp[id].r;
+            pk.sphere_meta[2 * (size_t)pos] = sp[id].mat;
+            pk.sphere_meta[2 * (size_t)pos + 1] = id;
+            leaf_refs[p] = lbvh::make_leaf_ref(0, pos);
+        } else {
+            int pos = p - sphere_pos[p];
+            const PlaneIn& q = pl[id - S];
+            float* o = &pk.planes[20 * (size_t)pos];
+            o[0] = q.n[0]; o[1] = q.n[1]; o[2] = q.n[2]; o[3] = q.D;
+            o[4] = q.w[0]; o[5] = q.w[1]; o[6] = q.w[2]; o[7] = i2f(q.type);
+            o[8] = q.u[0]; o[9] = q.u[1]; o[10] = q.u[2]; o[11] = i2f(q.mat);
+            o[12] = q.v[0]; o[13] = q.v[1]; o[14] = q.v[2]; o[15] = i2f(id - S);
+            o[16] = q.base[0]; o[17] = q.base[1]; o[18] = q.base[2]; o[19] = 0.f;
+            leaf_refs[p] = lbvh::make_leaf_ref(1, pos);
+        }
+    }
+    std::vector<int2> children(n);
+    std::vector<int> parent(2 * (size_t)n, -1);
+    for (int i = 0; i < n - 1; ++i) {  // k_radix
+        int l, r;
+        lbvh::radix_node(skeys.data(), n, i, l, r);
+        children[i] = make_int2(l, r);
+        parent[l] = i;
+        parent[r] = i;
+    }
+    std::vector<unsigned> arrived(n, 0);
+    for (int p = 0; p < n && n > 1; ++p) {  // k_fit
+        int cur = parent[(n - 1) + p];
+        while (true) {
+            if (arrived[cur]++ == 0) break;
+            boxes[cur] = lbvh::box_union(boxes[children[cur].x], boxes[children[cur].y]);
+            if (cur == 0) break;
+            cur = parent[cur];
+        }
+    }
+    std::vector<int> cur_items{0}, next_items;
+    std::vector<int> level_base, level_count;
+    int base = 0;
+    while (!cur_items.empty()) {  // k_collapse_count + scan + k_collapse_write
+        int count = (int)cur_items.size();
+        level_base.push_back(base);
+        level_count.push_back(count);
+        std::vector<int> kids(4 * (size_t)count), cnt(count), off(count);
+        for (int k = 0; k < count; ++k) cnt[k] = lbvh::collapse_pick(children.data(), boxes.data(), n, cur_items[k], &kids[4 * (size_t)k]);
+        int total = 0;
+        for (int k = 0; k < count; ++k) { off[k] = total; total += cnt[k]; }
+        out.nodes.resize((size_t)base + count);
+        next_items.assign(total, -1);
+        for (int k = 0; k < count; ++k)
+            lbvh::collapse_write(boxes.data(), leaf_refs.data(), n, &kids[4 * (size_t)k], base + count, off[k],
+                                 reinterpret_cast<float*>(&out.nodes[(size_t)base + k]), next_items.data());
+        base += count;
+        cur_items.swap(next_items);
+    }
+    std::vector<int> dep(out.nodes.size(), 0), need(out.nodes.size(), 0);
+    for (int l = (int)level_base.size() - 1; l >= 0; --l)  // k_depth
+        for (int k = 0; k < level_count[l]; ++k) {
+            int w = level_base[l] + k;
+            lbvh::depth_need(reinterpret_cast<const float*>(&out.nodes[w]), dep.data(), need.data(), dep[w], need[w]);
+        }
+    out.depth = dep[0];
+    out.max_stack = need[0];
+    out.leaves = n;
+    out.sphere_order.resize(S);
+    out.plane_order.resize(P);
+    for (int k = 0; k < S; ++k) out.sphere_order[k] = pk.sphere_meta[2 * (size_t)k + 1];
+    for (int k = 0; k < P; ++k) { int v; memcpy(&v, &pk.planes[20 * (size_t)k + 15], 4); out.plane_order[k] = v; }
+}
+
 extern "C" {
 
+// builder: 0 host binned-SAH (wide_bvh.cpp), 1 the device builder's steps run on the host (lbvh_build_host)
+int emu_scene_create2(const void* sp, int S, const void* pl, int P, const void* mt, int M, const float* tex, int tw, int th,
+                      int tex_mat, int builder, void** out);
 int emu_scene_create(const void* sp, int S, const void* pl, int P, const void* mt, int M, const float* tex, int tw, int th,
                      int tex_mat, void** out) {
+    return emu_scene_create2(sp, S, pl, P, mt, M, tex, tw, th, tex_mat, 0, out);
+}
+
+// structural soundness + stats of the device builder's tree: out = nodes, depth, max_stack, leaves; also checks that
+// lbvh::prim_box reproduces make_prim_boxes bit for bit (return 100 + axis if not)
+int emu_lbvh_check(const void* sp, int S, const void* pl, int P, int* out4) {
+    std::vector<PrimBox> prims = make_prim_boxes((const SphereIn*)sp, S, (const PlaneIn*)pl, P);
+    for (int i = 0; i < S + P; ++i) {
+        lbvh::Box b = lbvh::prim_box((const SphereIn*)sp, S, (const PlaneIn*)pl, i);
+        for (int a = 0; a < 3; ++a)
+            if (memcmp(&b.lo[a], &prims[i].lo[a], 4) || memcmp(&b.hi[a], &prims[i].hi[a], 4)) return 100 + a;
+    }
+    PackedScene pk;
+    lbvh_build_host((const SphereIn*)sp, S, (const PlaneIn*)pl, P, pk);
+    out4[0] = (int)pk.bvh.nodes.size(); out4[1] = pk.bvh.depth; out4[2] = pk.bvh.max_stack; out4[3] = pk.bvh.leaves;
+    return validate_wide_bvh(pk.bvh, prims);
+}
+
+int emu_scene_create2(const void* sp, int S, const void* pl, int P, const void* mt, int M, const float* tex, int tw, int th,
+                      int tex_mat, int builder, void** out) {
     EmuScene* s = new EmuScene();
     s->pk = pack_scene((const SphereIn*)sp, S, (const PlaneIn*)pl, P, (const MatIn*)mt, M);
+    if (builder == 1) lbvh_build_host((const SphereIn*)sp, S, (const PlaneIn*)pl, P, s->pk);
     s->dev.nodes = (const float4*)s->pk.bvh.nodes.data();
     s->dev.spheres = (const float4*)s->pk.spheres.data();
     s->dev.sphere_meta = (const int2*)s->pk.sphere_meta.data();

@@ -1,0 +1,123 @@
+"""Device BVH build (csrc/bvh_gpu.cu) on the GPU, through the C-ABI (rt_scene_create_ex with
+RT_BVH_GPU_LBVH): the closest hit does not depend on the tree, so every parity gate of the host-built scene must hold
+unchanged -- ids and t bit-exact against the oracle / golden fixtures, reference-stream frames bit-identical -- and the
+tree the kernels produce must be the tree the same per-element steps produce on the host (tests/emul)."""
+import numpy as np
+import pytest
+from conftest import bits, golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_scene(rt, sp, pl, mt, tex=None, tex_mat=-1):
+    return rt.Scene(sp, pl, mt, tex, tex_mat, bvh_builder=rt.BVH_GPU_LBVH)
+
+
+def test_lbvh_primary_ids_bit_exact_golden(rt):
+    g = golden("test_config_frame.npz")
+    sc = _gpu_scene(rt, g["spheres"], g["planes"], g["materials"])
+    assert sc.stats()["bvh_builder"] == rt.BVH_GPU_LBVH
+    rays = rt.pixel_center_rays(g["camera"])
+    ty, ix, t = sc.trace_primary(rays)
+    assert (ty == g["type_brute"]).all() and (ix == g["index_brute"]).all()
+    hit = ty >= 0
+    assert (bits(t[hit]) == bits(g["t_brute"][hit])).all()
+    # whole frame on the reference's RNG stream: same gate as the host-built scene (>= 99.95 % of pixels bit-identical)
+    fb, info = sc.render(g["camera"], rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    same = (bits(fb) == bits(g["fb_sum"])).all(-1).mean()
+    assert info["segments"] == int(g["segments"][0]) and same >= 0.9995, same
+    sc.close()
+    g = golden("synthetic2k_textured.npz")
+    sp, pl, mt, _ = rt.synthetic_scene(2000, seed=1234).arrays()
+    sc = _gpu_scene(rt, sp, pl, mt)
+    ty, ix, t = sc.trace_primary(rt.pixel_center_rays(g["trace_camera"]))
+    assert (ty == g["type_brute"]).all() and (ix == g["index_brute"]).all()
+    hit = ty >= 0
+    assert (bits(t[hit]) == bits(g["t_brute"][hit])).all()
+    sc.close()
+
+
+@pytest.mark.parametrize("n", [10000, 100000])
+def test_lbvh_equals_host_built_scene(rt, orc, n):
+    """same ids / t / reference-stream frame as the host-SAH scene, and as the oracle's linear scan on a sample"""
+    hs = rt.synthetic_scene(n, W=192, H=108, sqrt_spp=2, depth=8, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    a = rt.Scene(sp, pl, mt)
+    b = _gpu_scene(rt, sp, pl, mt)
+    cam = rt.build_camera(270, 480, [-15, 0, 4.5], [0, 0, 4.5], 90.0, 1, 1)
+    rays = rt.pixel_center_rays(cam)
+    ta, tb = a.trace_primary(rays), b.trace_primary(rays)
+    assert (ta[0] == tb[0]).all() and (ta[1] == tb[1]).all() and (bits(ta[2]) == bits(tb[2])).all()
+    sel = np.arange(0, len(rays), 211)
+    ly, li, _ = orc.scene(sp, pl, mt).trace(rays[sel], 0)
+    assert (tb[0][sel] == ly).all() and (tb[1][sel] == li).all()
+    fa, ia = a.render(hs.camera(0), rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    fb, ib = b.render(hs.camera(0), rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    assert ia["segments"] == ib["segments"] and fa.tobytes() == fb.tobytes()
+    # production stream: fast-math ties may resolve differently between trees; the frames agree to fp32 noise
+    pa, ja = a.render(hs.camera(0), seed=3)
+    pb, jb = b.render(hs.camera(0), seed=3)
+    assert abs(ja["segments"] - jb["segments"]) <= 1e-3 * ja["segments"]
+    assert (bits(pa) == bits(pb)).all(-1).mean() > 0.99
+    sa, sb = a.stats(), b.stats()
+    print("n=%d host SAH: %d nodes depth %d build %.2f ms | device LBVH: %d nodes depth %d stack %d build %.3f ms (+%.3f ms input upload)"
+          % (n, sa["wide_nodes"], sa["wide_depth"], sa["build_ms"], sb["wide_nodes"], sb["wide_depth"], sb["max_stack"], sb["build_ms"],
+             sb["input_upload_ms"]))
+    assert sb["leaves"] == len(sp) + len(pl) and sb["max_stack"] <= 64
+    a.close()
+    b.close()
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 7, 500, 20000])
+def test_lbvh_device_tree_is_the_emulated_tree(rt, emul, n):
+    """the kernels and the host loops over the same per-element functions (lbvh.cuh) build the same tree"""
+    hs = rt.synthetic_scene(n, seed=11)
+    sp, pl, mt, _ = hs.arrays()
+    out = np.zeros(4, np.int32)
+    assert emul.emu_lbvh_check(sp.ctypes.data, len(sp), pl.ctypes.data, len(pl), out.ctypes.data) == 0
+    sc = _gpu_scene(rt, sp, pl, mt)
+    st = sc.stats()
+    assert [st["wide_nodes"], st["wide_depth"], st["max_stack"], st["leaves"]] == list(out), (st, out)
+    sc.close()
+
+
+def test_lbvh_edge_cases(rt):
+    mt = np.zeros(1, rt.MATERIAL)
+    rays = np.array([[0, 0, 0, 0, 0, -1], [0.2, 0, 0, 0, 0, -1], [5, 5, 0, 0, 0, -1]], np.float32)
+    # no primitives at all: every ray misses
+    sc = _gpu_scene(rt, np.zeros(0, rt.SPHERE), np.zeros(0, rt.PLANE), mt)
+    ty, ix, t = sc.trace_primary(rays)
+    assert (ty == -1).all()
+    sc.close()
+    # one sphere; then 37 identical spheres (equal Morton keys): the reference's linear scan keeps the LAST of equal hits
+    sp = np.zeros(1, rt.SPHERE)
+    sp["center"] = [0, 0, -5]
+    sp["radius"] = 1
+    sc = _gpu_scene(rt, sp, np.zeros(0, rt.PLANE), mt)
+    ty, ix, t = sc.trace_primary(rays)
+    assert list(ty) == [0, 0, -1] and ix[0] == 0 and t[0] == 4.0
+    sc.close()
+    dup = np.repeat(sp, 37)
+    a = rt.Scene(dup, np.zeros(0, rt.PLANE), mt)
+    b = _gpu_scene(rt, dup, np.zeros(0, rt.PLANE), mt)
+    ra, rb = a.trace_primary(rays), b.trace_primary(rays)
+    assert (ra[0] == rb[0]).all() and (ra[1] == rb[1]).all() and (bits(ra[2]) == bits(rb[2])).all()
+    assert rb[1][0] == 36
+    a.close()
+    b.close()
+
+
+def test_lbvh_build_is_deterministic_and_fast_at_full_size(rt):
+    """1M spheres (BASELINE configs[3] primitive count): two builds give the same frame; build time is reported"""
+    hs = rt.synthetic_scene(1000000, W=256, H=144, sqrt_spp=1, depth=8, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    a = _gpu_scene(rt, sp, pl, mt)
+    b = _gpu_scene(rt, sp, pl, mt)
+    fa, ia = a.render(hs.camera(0), seed=5)
+    fb, ib = b.render(hs.camera(0), seed=5)
+    assert fa.tobytes() == fb.tobytes() and ia["segments"] == ib["segments"]
+    st = b.stats()
+    print("1M spheres: device build %.3f ms, %d nodes, depth %d, stack %d" % (st["build_ms"], st["wide_nodes"], st["wide_depth"], st["max_stack"]))
+    assert st["max_stack"] <= 64 and st["build_ms"] < 200.0
+    a.close()
+    b.close()

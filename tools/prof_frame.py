@@ -23,11 +23,12 @@ def main():
     ap.add_argument("--count", action="store_true")
     ap.add_argument("--top-nodes", type=int, default=-1)
     ap.add_argument("--frame", type=int, default=0)
+    ap.add_argument("--builder", default="host", choices=["host", "gpu"], help="BVH builder: host binned SAH / device LBVH")
     ap.add_argument("--chunk", type=int, default=0, help="sample_chunk option (0 auto, -1 whole pixels)")
     a = ap.parse_args()
     cfg = rt.CONFIGS[a.workload]
     hs = rt.synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
-    scene = rt.Scene.from_host(hs)
+    scene = rt.Scene.from_host(hs, bvh_builder=rt.BVH_GPU_LBVH if a.builder == "gpu" else rt.BVH_HOST_SAH)
     cam = hs.camera(a.frame)
     if a.spp:
         cam["samples_per_pixel"] = a.spp
