@@ -107,7 +107,17 @@ __global__ void k_radix(const unsigned long long* __restrict__ keys, int n, int2
 }
 
 // ---- 5. bottom-up fit: the second thread to arrive at an inner node owns it
-__global__ void k_fit(const int2* __restrict__ children, const int* __restrict__ parent, int n, Box* boxes, unsigned int* arrived) {
+__device__ __forceinline__ lbvh::CollapseDp load_dp(const lbvh::CollapseDp* dp, int node, int n) {
+    if (node >= n - 1) return lbvh::dp_leaf();
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(dp + node));
+    lbvh::CollapseDp d;
+    d.c[0] = v.x; d.c[1] = v.y; d.c[2] = v.z;
+    d.k = __float_as_uint(v.w);
+    return d;
+}
+// the same thread fills the node's collapse table (lbvh.cuh, step 5b) from its children's
+__global__ void k_fit(const int2* __restrict__ children, const int* __restrict__ parent, int n, Box* boxes, lbvh::CollapseDp* dp,
+                      unsigned int* arrived) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n || n < 2) return;
     int cur = parent[(n - 1) + p];
@@ -124,18 +134,20 @@ __global__ void k_fit(const int2* __restrict__ children, const int* __restrict__
             u.hi[k] = fmaxf(__ldcg(a + 3 + k), __ldcg(b + 3 + k));
         }
         boxes[cur] = u;
+        const lbvh::CollapseDp d = lbvh::dp_inner(load_dp(dp, ch.x, n), load_dp(dp, ch.y, n), lbvh::box_area(u));
+        *reinterpret_cast<float4*>(dp + cur) = make_float4(d.c[0], d.c[1], d.c[2], __uint_as_float(d.k));
         if (cur == 0) return;
         cur = parent[cur];
     }
 }
 
 // ---- 6. collapse, one breadth-first level per launch pair
-__global__ void k_collapse_count(const int2* __restrict__ children, const Box* __restrict__ boxes, int n,
+__global__ void k_collapse_count(const int2* __restrict__ children, const lbvh::CollapseDp* __restrict__ dp, int n,
                                  const int* __restrict__ items, int count, int4* __restrict__ kids_out, int* __restrict__ inner_cnt) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= count) return;
     int kids[4];
-    inner_cnt[k] = lbvh::collapse_pick(children, boxes, n, items[k], kids);
+    inner_cnt[k] = lbvh::collapse_pick_dp(children, dp, n, items[k], kids);
     kids_out[k] = make_int4(kids[0], kids[1], kids[2], kids[3]);
 }
 __global__ void k_collapse_write(const Box* __restrict__ boxes, const int* __restrict__ leaf_refs, int n,
@@ -251,7 +263,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     size_t need = pad256((size_t)n * sizeof(Box)) + 2 * pad256((size_t)n * 8) + 2 * pad256((size_t)n * 4) +  // prim boxes, keys x2, vals x2
                   pad256((size_t)(2 * n) * sizeof(Box)) + pad256((size_t)n * 8) + pad256((size_t)(2 * n) * 4) +  // boxes, children, parent
                   8 * pad256((size_t)n * 4) +       // arrived, is_sphere, sphere_pos, leaf_refs, items x2, inner_cnt, inner_off
-                  pad256((size_t)n * 16) +          // kids
+                  2 * pad256((size_t)n * 16) +      // kids, collapse tables
                   2 * pad256((size_t)max_nodes * 4) +  // dep, need
                   pad256(sort_tmp) + pad256(scan_tmp) + 4 * 256;
     BG_CUDA(cudaMalloc((void**)&arena.base, need));
@@ -273,6 +285,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     int* inner_cnt = arena.take<int>(n);
     int* inner_off = arena.take<int>(n);
     int4* kids = arena.take<int4>(n);
+    lbvh::CollapseDp* dp = arena.take<lbvh::CollapseDp>(n);
     int* dep = arena.take<int>(max_nodes);
     int* need_s = arena.take<int>(max_nodes);
     void* d_sort_tmp = arena.take<char>(sort_tmp);
@@ -297,7 +310,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
                                                   (float4*)r.d_spheres, (int2*)r.d_sphere_meta, (float4*)r.d_planes);
     if (n > 1) {
         k_radix<<<blocks_for(n - 1), kThreads, 0, stream>>>(keys_b, n, children, parent);
-        k_fit<<<blocks_for(n), kThreads, 0, stream>>>(children, parent, n, boxes, arrived);
+        k_fit<<<blocks_for(n), kThreads, 0, stream>>>(children, parent, n, boxes, dp, arrived);
     }
     BG_CUDA(cudaGetLastError());
 
@@ -314,7 +327,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
         if (base + count > max_nodes) { r.fail_line = __LINE__; BG_CUDA(cudaErrorUnknown); }
         level_base.push_back(base);
         level_count.push_back(count);
-        k_collapse_count<<<blocks_for(count), kThreads, 0, stream>>>(children, boxes, n, cur, count, kids, inner_cnt);
+        k_collapse_count<<<blocks_for(count), kThreads, 0, stream>>>(children, dp, n, cur, count, kids, inner_cnt);
         BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, inner_cnt, inner_off, count, stream));
         k_collapse_write<<<blocks_for(count), kThreads, 0, stream>>>(boxes, leaf_refs, n, cur, kids, inner_off, inner_cnt, count, base,
                                                                     (float*)r.d_nodes, nxt, next_count, prim_cost, sah);

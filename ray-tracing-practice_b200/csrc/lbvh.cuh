@@ -10,8 +10,9 @@
 //     3. radix sort of (key, primitive)
 //     4. binary radix tree over the sorted keys, one thread per inner node (Karras 2012), ties broken by position
 //     5. bottom-up box fit (second arrival at a node computes it)
-//     6. breadth-first collapse to the 128-byte 4-wide nodes the render kernels read (same slot rules as the host
-//        builder: open the child with the largest surface area until 4 slots are used; one primitive per leaf)
+//     6. breadth-first collapse to the 128-byte 4-wide nodes the render kernels read; which binary nodes become wide
+//        nodes is decided by the same dynamic programme as in the host builder (tables filled in step 5); one primitive
+//        per leaf
 //     7. per-node depth / worst-case stack need, swept level by level from the leaves up
 // Every step is a function of one element, written once here and called from the kernels in bvh_gpu.cu and -- for the
 // CPU test tier -- from tests/emul, which runs them in plain loops and checks the tree with validate_wide_bvh.
@@ -205,6 +206,70 @@ LB_HD int collapse_pick(const int2* children, const Box* boxes, int n, int bin, 
         int open = kids[pick];
         kids[pick] = children[open].x;
         kids[nk++] = children[open].y;
+    }
+    int inner = 0;
+    for (int k = 0; k < nk; ++k) inner += kids[k] < n - 1;
+    return inner;
+}
+
+// ---- step 5b/6b: WHICH binary nodes become wide nodes, chosen by the same dynamic programme as the host builder
+// (wide_bvh.cpp; after Ylitie, Karras, Laine, HPG 2017, section 4.1).  With one primitive per leaf the leaf term of the SAH
+// is the same for every collapse, so the cost to minimise is the summed area of the wide nodes:
+//     c[0] = area(n) + min_k (cl[k-1] + cr[3-k]),  k = 1..3 roots from the left subtree, 4-k from the right
+//     c[i] = min(c[i-1], min_k (cl[k-1] + cr[i-k]))     subtree n represented by at most i+1 roots (k = 0: "use fewer")
+// The table of a node is filled by the thread that fits its box (bottom-up), 16 bytes per inner node; leaves cost 0.
+struct alignas(16) CollapseDp {
+    float c[3];
+    uint32_t k;  // choice for i roots in bits 8*i .. 8*i+7
+};
+LB_HD CollapseDp dp_leaf() {
+    CollapseDp d;
+    d.c[0] = d.c[1] = d.c[2] = 0.f;
+    d.k = 0;
+    return d;
+}
+LB_HD CollapseDp dp_inner(const CollapseDp& l, const CollapseDp& r, float area) {
+    CollapseDp d;
+    float best = LB_ADD(l.c[0], r.c[2]);
+    uint32_t bk = 1;
+    for (int k = 2; k <= 3; ++k) {
+        float c = LB_ADD(l.c[k - 1], r.c[3 - k]);
+        if (c < best) { best = c; bk = (uint32_t)k; }
+    }
+    d.c[0] = LB_ADD(area, best);
+    d.k = bk;
+    for (int i = 1; i < 3; ++i) {
+        float bi = d.c[i - 1];
+        uint32_t ki = 0;
+        for (int k = 1; k <= i; ++k) {
+            float c = LB_ADD(l.c[k - 1], r.c[i - k]);
+            if (c < bi) { bi = c; ki = (uint32_t)k; }
+        }
+        d.c[i] = bi;
+        d.k |= ki << (8 * i);
+    }
+    return d;
+}
+// kids of the wide node rooted at binary inner node `bin` according to the tables; returns the number of INNER kids
+LB_HD int collapse_pick_dp(const int2* children, const CollapseDp* dp, int n, int bin, int kids[4]) {
+    int nk = 0;
+    kids[0] = kids[1] = kids[2] = kids[3] = -1;
+    if (n == 1) {
+        kids[0] = 0;
+        return 0;
+    }
+    int st_node[4], st_roots[4], sp = 0;
+    const int kl = (int)(dp[bin].k & 0xffu);
+    st_node[sp] = children[bin].y; st_roots[sp++] = 4 - kl;
+    st_node[sp] = children[bin].x; st_roots[sp++] = kl;
+    while (sp > 0) {
+        --sp;
+        const int node = st_node[sp], roots = st_roots[sp];
+        if (node >= n - 1 || roots <= 1) { kids[nk++] = node; continue; }
+        const int k = (int)((dp[node].k >> (8 * (roots - 1))) & 0xffu);
+        if (k == 0) { st_node[sp] = node; st_roots[sp++] = roots - 1; continue; }
+        st_node[sp] = children[node].y; st_roots[sp++] = roots - k;
+        st_node[sp] = children[node].x; st_roots[sp++] = k;
     }
     int inner = 0;
     for (int k = 0; k < nk; ++k) inner += kids[k] < n - 1;

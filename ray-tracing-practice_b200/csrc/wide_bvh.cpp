@@ -6,6 +6,8 @@
 #include "wide_bvh.h"
 
 #include <algorithm>
+#include <array>
+#include <functional>
 #include <atomic>
 #include <cmath>
 #include <cstring>
@@ -219,6 +221,50 @@ WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf) {
         }
     }
 
+    // Which binary nodes become wide nodes: dynamic programme over the binary tree (after Ylitie, Karras, Laine, "Efficient
+    // incoherent ray traversal on GPUs through compressed wide BVHs", HPG 2017, section 4.1).  With one primitive per leaf the
+    // leaf term of the SAH is the same for every collapse, so the cost to minimise is the summed area of the wide nodes:
+    //   c[n][0] = area(n) + min_k (c[l][k-1] + c[r][3-k]),  k = 1..3 roots from the left subtree, 4-k from the right
+    //   c[n][i] = min(c[n][i-1], min_k (c[l][k-1] + c[r][i-k]))      subtree n represented by at most i+1 roots
+    // Children have larger indices than their parents (alloc order), so a descending sweep is a post-order.
+    static const bool use_dp = !(getenv("RTB_COLLAPSE") && atoi(getenv("RTB_COLLAPSE")) == 0);
+    const int nbin = B.next_node.load();
+    std::vector<std::array<float, 3>> cost(use_dp ? nbin : 0);
+    std::vector<std::array<unsigned char, 3>> choice(use_dp ? nbin : 0);
+    if (use_dp) {
+        for (int n = nbin - 1; n >= 0; --n) {
+            const BinNode& b = bn[n];
+            if (b.left < 0) { cost[n] = {0.f, 0.f, 0.f}; choice[n] = {0, 0, 0}; continue; }
+            const auto &cl = cost[b.left], &cr = cost[b.right];
+            float best = std::numeric_limits<float>::infinity();
+            int bk = 1;
+            for (int k = 1; k <= 3; ++k) {
+                float c = cl[k - 1] + cr[3 - k];
+                if (c < best) { best = c; bk = k; }
+            }
+            cost[n][0] = b.box.area() + best;
+            choice[n][0] = (unsigned char)bk;
+            for (int i = 1; i < 3; ++i) {  // at most i+1 roots
+                float bi = cost[n][i - 1];
+                int ki = 0;
+                for (int k = 1; k <= i; ++k) {
+                    float c = cl[k - 1] + cr[i - k];
+                    if (c < bi) { bi = c; ki = k; }
+                }
+                cost[n][i] = bi;
+                choice[n][i] = (unsigned char)ki;
+            }
+        }
+    }
+    // the (at most `roots`) forest roots that represent binary subtree n
+    std::function<void(int, int, int*, int&)> gather = [&](int n, int roots, int* kids, int& nk) {
+        if (bn[n].left < 0 || roots <= 1) { kids[nk++] = n; return; }
+        int k = choice[n][roots - 1];
+        if (k == 0) { gather(n, roots - 1, kids, nk); return; }
+        gather(bn[n].left, k, kids, nk);
+        gather(bn[n].right, roots - k, kids, nk);
+    };
+
     // breadth-first collapse
     struct Item { int bin; int wide; };
     std::deque<Item> q;
@@ -233,6 +279,9 @@ WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf) {
         int nk = 0;
         if (bn[it.bin].left < 0) {
             kids[nk++] = it.bin;  // single-leaf scene
+        } else if (use_dp) {
+            gather(bn[it.bin].left, choice[it.bin][0], kids, nk);
+            gather(bn[it.bin].right, 4 - choice[it.bin][0], kids, nk);
         } else {
             kids[nk++] = bn[it.bin].left;
             kids[nk++] = bn[it.bin].right;

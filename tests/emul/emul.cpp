@@ -94,15 +94,19 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
         parent[r] = i;
     }
     std::vector<unsigned> arrived(n, 0);
+    std::vector<lbvh::CollapseDp> dp(n);
     for (int p = 0; p < n && n > 1; ++p) {  // k_fit
         int cur = parent[(n - 1) + p];
         while (true) {
             if (arrived[cur]++ == 0) break;
-            boxes[cur] = lbvh::box_union(boxes[children[cur].x], boxes[children[cur].y]);
+            const int l = children[cur].x, r = children[cur].y;
+            boxes[cur] = lbvh::box_union(boxes[l], boxes[r]);
+            dp[cur] = lbvh::dp_inner(l >= n - 1 ? lbvh::dp_leaf() : dp[l], r >= n - 1 ? lbvh::dp_leaf() : dp[r], lbvh::box_area(boxes[cur]));
             if (cur == 0) break;
             cur = parent[cur];
         }
     }
+    static const bool greedy = getenv("RTB_LBVH_COLLAPSE") && atoi(getenv("RTB_LBVH_COLLAPSE")) == 0;
     std::vector<int> cur_items{0}, next_items;
     std::vector<int> level_base, level_count;
     int base = 0;
@@ -111,7 +115,9 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
         level_base.push_back(base);
         level_count.push_back(count);
         std::vector<int> kids(4 * (size_t)count), cnt(count), off(count);
-        for (int k = 0; k < count; ++k) cnt[k] = lbvh::collapse_pick(children.data(), boxes.data(), n, cur_items[k], &kids[4 * (size_t)k]);
+        for (int k = 0; k < count; ++k)
+            cnt[k] = greedy ? lbvh::collapse_pick(children.data(), boxes.data(), n, cur_items[k], &kids[4 * (size_t)k])
+                            : lbvh::collapse_pick_dp(children.data(), dp.data(), n, cur_items[k], &kids[4 * (size_t)k]);
         int total = 0;
         for (int k = 0; k < count; ++k) { off[k] = total; total += cnt[k]; }
         out.nodes.resize((size_t)base + count);
