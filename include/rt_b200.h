@@ -138,6 +138,9 @@ unsigned long long rt_tiles_packed_floats(int width, int height, int nranks); /*
 
 const char* rt_last_error(void);
 int rt_device_count(void);
+/* Selects the CUDA device of the CALLING THREAD for subsequent rt_scene_create calls (a scene lives on the device it was
+ * created on).  The reference is single-GPU (it never calls cudaSetDevice); this is what the multi-GPU frame loop uses. */
+int rt_set_device(int device);
 const char* rt_version(void);
 
 #ifdef __cplusplus

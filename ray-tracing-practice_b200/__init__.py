@@ -40,7 +40,7 @@ TILE = 16
 
 C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
                  "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
-                 "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_version"]
+                 "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_set_device", "rt_version"]
 
 
 class RtError(RuntimeError):

@@ -94,6 +94,13 @@ int rt_device_count(void) {
     return n;
 }
 
+int rt_set_device(int device) {
+    int rc = check_device();
+    if (rc) return rc;
+    RT_CUDA(cudaSetDevice(device));
+    return RT_OK;
+}
+
 static int upload(void** dst, const void* src, size_t bytes, unsigned long long& total) {
     *dst = nullptr;
     size_t alloc = bytes ? bytes : 16;

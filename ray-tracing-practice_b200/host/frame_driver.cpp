@@ -8,7 +8,10 @@
 #include <condition_variable>
 #include <cstdio>
 #include <mutex>
+#include <algorithm>
+#include <cstdlib>
 #include <ostream>
+#include <sstream>
 #include <string>
 #include <thread>
 #include <vector>
@@ -69,7 +72,10 @@ struct Writer {
 };
 }  // namespace
 
-int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::ostream& log) {
+// One device's share of the frame loop: frames first, first+stride, ... on the CURRENT device (the caller selected it).
+// Log lines go to lines[n]; the caller prints them in frame order.
+static int render_frames_on_device(const SceneParams& p, const HostScene& scene, int format, int first, int stride,
+                                   std::vector<std::string>& lines) {
     rt_scene* h = nullptr;
     const float* tex = scene.texels.empty() ? nullptr : scene.texels.data();
     int rc = rt_scene_create(scene.spheres.data(), (int)scene.spheres.size(), scene.planes.data(), (int)scene.planes.size(),
@@ -84,7 +90,7 @@ int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::os
     {
         Writer writer;
         std::vector<unsigned char> rgb;
-        for (int n = 0; n < p.num_frames; ++n) {
+        for (int n = first; n < p.num_frames; n += stride) {
             char filename[256];
             std::snprintf(filename, sizeof filename, p.output_path.c_str(), n);
             CameraImage cam = camera_for_frame(p, n);
@@ -100,11 +106,48 @@ int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::os
             writer.submit(rgb, filename, p.width, p.height, format);
             float ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
             long long total_rays = (long long)p.width * p.height * p.render.sqrt_rays_per_pixel * p.render.sqrt_rays_per_pixel;
-            log << n << "\t" << ms << "\t" << total_rays << "\n";
+            std::ostringstream os;
+            os << n << "\t" << ms << "\t" << total_rays << "\n";
+            lines[n] = os.str();
         }
     }  // ~Writer: the last file is on disk before we return
     rt_scene_destroy(h);
     return status;
+}
+
+// Frames are independent (src/camera.cu:297-347 renders them one after the other): with num_gpus > 1 device g renders
+// frames g, g+num_gpus, ... from its own copy of the scene, each with its own writer thread; the stdout lines come out in
+// frame order once all devices are done.  num_gpus <= 0: RTB_GPUS from the environment, else 1.
+int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::ostream& log, int num_gpus) {
+    if (num_gpus <= 0) {
+        const char* e = std::getenv("RTB_GPUS");
+        num_gpus = e ? std::atoi(e) : 1;
+    }
+    const int have = rt_device_count();
+    if (have < 1) {
+        std::fprintf(stderr, "rt_b200: no CUDA device\n");
+        return 99;
+    }
+    // more workers than devices is allowed (worker g uses device g % have): it only costs memory, and it lets a one-GPU box
+    // run the same threaded path
+    num_gpus = std::max(1, std::min(num_gpus, std::max(p.num_frames, 1)));
+    std::vector<std::string> lines((size_t)std::max(p.num_frames, 0));
+    std::vector<int> status((size_t)num_gpus, 0);
+    if (num_gpus == 1) {
+        status[0] = render_frames_on_device(p, scene, format, 0, 1, lines);
+    } else {
+        std::vector<std::thread> th;
+        for (int g = 0; g < num_gpus; ++g)
+            th.emplace_back([&, g] {
+                if (rt_set_device(g % have) != RT_OK) { std::fprintf(stderr, "%s\n", rt_last_error()); status[g] = 99; return; }
+                status[g] = render_frames_on_device(p, scene, format, g, num_gpus, lines);
+            });
+        for (auto& t : th) t.join();
+    }
+    for (const std::string& l : lines) log << l;
+    for (int s : status)
+        if (s) return s;
+    return 0;
 }
 
 }  // namespace rtb

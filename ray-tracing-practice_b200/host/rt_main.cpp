@@ -2,7 +2,7 @@
 // `--cpu` is refused: this build has no CPU render path (the reference's --cpu lives on as oracle/_ref).
 // Extensions (all optional, after the mode): --png | --ppm choose the saver the reference ships but never wires up;
 // --spheres N [--seed S] appends the seeded N-sphere field of BASELINE.json's configs 2-4; --bvh-gpu builds the BVH on
-// the device instead of on the host.
+// the device instead of on the host; --gpus N renders the frames of the camera path on N devices.
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -12,7 +12,7 @@
 
 int main(int argc, char** argv) {
     using namespace rtb;
-    int format = 0, spheres = 0;
+    int format = 0, spheres = 0, gpus = 0;
     unsigned seed = 1234;
     bool want_default = false;
     for (int i = 1; i < argc; ++i) {
@@ -24,6 +24,7 @@ int main(int argc, char** argv) {
         else if (a == "--ppm") format = 2;
         else if (a == "--spheres" && i + 1 < argc) spheres = std::atoi(argv[++i]);
         else if (a == "--bvh-gpu") setenv("RTB_BVH_BUILDER", "gpu", 1);  // device BVH build (rt_scene_create_ex, RT_BVH_GPU_LBVH)
+        else if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);  // frames n % gpus == g render on device g
         else if (a == "--seed" && i + 1 < argc) seed = (unsigned)std::strtoul(argv[++i], nullptr, 10);
     }
     if (want_default) { std::cout << default_config_text(); return 0; }
@@ -33,5 +34,5 @@ int main(int argc, char** argv) {
     if (!create_scene(params, scene, true, &err)) { std::cerr << err << std::endl; return 1; }
     if (!err.empty()) std::cerr << err << std::endl;
     if (spheres > 0) make_synthetic_spheres(scene, spheres, seed);
-    return gpu_render(params, scene, format, std::cout);
+    return gpu_render(params, scene, format, std::cout, gpus);
 }

@@ -96,6 +96,8 @@ bool load_texels(const std::string& path, std::vector<float>& rgba, int& w, int&
 
 // gpu_render (src/camera.cu:290-349): every frame through the C-ABI; prints "n\tms\ttotal_rays" per frame.
 // format: 0 binary (the reference's default), 1 png, 2 text ppm.  Returns 0, or 99 like check_cuda's exit code.
-int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::ostream& log);
+// num_gpus > 1 distributes the (independent) frames over that many devices of the box, frame n on device n % num_gpus;
+// 0 = take RTB_GPUS from the environment, default 1.
+int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::ostream& log, int num_gpus = 0);
 
 }  // namespace rtb

@@ -245,6 +245,20 @@ def test_gpu_render_driver_writes_reference_format(rt, tmp_path):
     assert raw[8:].max() > 0
 
 
+def test_gpu_render_driver_distributes_frames(rt, tmp_path, monkeypatch):
+    """frames of the camera path on several workers (RTB_GPUS; worker g -> device g % device_count): same files, log in frame order"""
+    def run(tag, gpus):
+        monkeypatch.setenv("RTB_GPUS", str(gpus))
+        hs = rt.HostScene(rt.test_config_text(W=64, H=40, sqrt_spp=2, max_depth=4, output=str(tmp_path / (tag + "_%d.bin")), num_frames=5), texture="")
+        log = hs.gpu_render(0)
+        return [l.split("\t")[0] for l in log.strip().split("\n")], [np.fromfile(tmp_path / ("%s_%d.bin" % (tag, n)), np.uint8) for n in range(5)]
+    order1, files1 = run("a", 1)
+    order3, files3 = run("b", 3)
+    assert order1 == order3 == ["0", "1", "2", "3", "4"]
+    assert all(a.tobytes() == b.tobytes() and len(a) == 8 + 64 * 40 * 3 for a, b in zip(files1, files3))
+    assert files1[0].tobytes() != files1[2].tobytes()  # the camera moves
+
+
 def test_sample_chunks_change_only_the_summation_grouping(rt, test_scene):
     """megakernel work items split a pixel's samples into chunks (shorter end-of-frame tail): same samples, same segment
     count, chunk sums added in chunk order => deterministic and equal to the unsplit frame up to fp32 re-association"""
