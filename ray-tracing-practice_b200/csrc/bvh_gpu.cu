@@ -8,7 +8,9 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
+#include <algorithm>
 #include <chrono>
+#include <cstring>
 #include <cstdlib>
 #include <vector>
 
@@ -21,11 +23,11 @@ using lbvh::Box;
 constexpr int kThreads = 256;
 inline int blocks_for(int n) { return (n + kThreads - 1) / kThreads; }
 
-// ---- 1. boxes + bounds of the box centres (ordered-uint atomics; bounds6 = min xyz, max xyz)
+// ---- 1. boxes + bounds (ordered-uint atomics): bounds12 = centre min xyz, centre max xyz, box min xyz, box max xyz
 __global__ void k_boxes(const SphereIn* __restrict__ sp, int S, const PlaneIn* __restrict__ pl, int n, Box* __restrict__ prim_boxes,
-                        unsigned int* __restrict__ bounds6) {
+                        unsigned int* __restrict__ bounds12) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned int mn[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[3] = {0u, 0u, 0u};
+    unsigned int mn[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu}, mx[6] = {0u, 0u, 0u, 0u, 0u, 0u};
     if (i < n) {
         Box b = lbvh::prim_box(sp, S, pl, i);
         prim_boxes[i] = b;
@@ -33,31 +35,54 @@ __global__ void k_boxes(const SphereIn* __restrict__ sp, int S, const PlaneIn* _
             unsigned int c = lbvh::float_to_ordered(__fmul_rn(0.5f, __fadd_rn(b.lo[a], b.hi[a])));
             mn[a] = c;
             mx[a] = c;
+            mn[3 + a] = lbvh::float_to_ordered(b.lo[a]);
+            mx[3 + a] = lbvh::float_to_ordered(b.hi[a]);
         }
     }
-    for (int a = 0; a < 3; ++a) {
+    for (int a = 0; a < 6; ++a) {
         mn[a] = __reduce_min_sync(0xffffffffu, mn[a]);
         mx[a] = __reduce_max_sync(0xffffffffu, mx[a]);
     }
     if ((threadIdx.x & 31) == 0) {
         for (int a = 0; a < 3; ++a) {
-            atomicMin(&bounds6[a], mn[a]);
-            atomicMax(&bounds6[3 + a], mx[a]);
+            atomicMin(&bounds12[a], mn[a]);
+            atomicMax(&bounds12[3 + a], mx[a]);
+            atomicMin(&bounds12[6 + a], mn[3 + a]);
+            atomicMax(&bounds12[9 + a], mx[3 + a]);
         }
     }
 }
 
-// ---- 2. Morton keys
-__global__ void k_keys(const Box* __restrict__ prim_boxes, int n, const unsigned int* __restrict__ bounds6,
+// ---- 1b. hoist candidates: primitives whose box has a large share of the scene box's area (rare: the floor quad).  The
+// host picks at most four of them (largest first) from this list.
+__global__ void k_hoist(const Box* __restrict__ prim_boxes, int n, const unsigned int* __restrict__ bounds12, int* __restrict__ cand_count,
+                        int2* __restrict__ cand) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Box sb;
+    for (int a = 0; a < 3; ++a) {
+        sb.lo[a] = lbvh::ordered_to_float(bounds12[6 + a]);
+        sb.hi[a] = lbvh::ordered_to_float(bounds12[9 + a]);
+    }
+    const Box b = prim_boxes[i];
+    if (lbvh::hoist_candidate(b, lbvh::box_area(sb))) {
+        int k = atomicAdd(cand_count, 1);
+        if (k < lbvh::kHoistCandCap) cand[k] = make_int2(i, __float_as_int(lbvh::box_area(b)));
+    }
+}
+
+// ---- 2. Morton keys; hoisted primitives get the largest key, so the sort puts them behind the tree's primitives
+__global__ void k_keys(const Box* __restrict__ prim_boxes, int n, const unsigned int* __restrict__ bounds12, int4 hoisted,
                        unsigned long long* __restrict__ keys, unsigned int* __restrict__ vals) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float cmin[3], cmax[3];
     for (int a = 0; a < 3; ++a) {
-        cmin[a] = lbvh::ordered_to_float(bounds6[a]);
-        cmax[a] = lbvh::ordered_to_float(bounds6[3 + a]);
+        cmin[a] = lbvh::ordered_to_float(bounds12[a]);
+        cmax[a] = lbvh::ordered_to_float(bounds12[3 + a]);
     }
-    keys[i] = lbvh::morton_key(prim_boxes[i], cmin, cmax);
+    const bool h = i == hoisted.x || i == hoisted.y || i == hoisted.z || i == hoisted.w;
+    keys[i] = h ? ~0ull : lbvh::morton_key(prim_boxes[i], cmin, cmax);
     vals[i] = (unsigned int)i;
 }
 
@@ -69,13 +94,13 @@ __global__ void k_flags(const unsigned int* __restrict__ vals, int n, int S, int
 
 // ---- 3c. leaf boxes, leaf references and the leaf-ordered SoA primitive streams (layouts of scene_pack.h)
 __global__ void k_pack(const SphereIn* __restrict__ sp, int S, const PlaneIn* __restrict__ pl, const unsigned int* __restrict__ vals,
-                       const int* __restrict__ sphere_pos, const Box* __restrict__ prim_boxes, int n, Box* __restrict__ boxes,
+                       const int* __restrict__ sphere_pos, const Box* __restrict__ prim_boxes, int n, int n_tree, Box* __restrict__ boxes,
                        int* __restrict__ leaf_refs, float4* __restrict__ spheres, int2* __restrict__ sphere_meta,
                        float4* __restrict__ planes) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int id = (int)vals[p];
-    boxes[(n - 1) + p] = prim_boxes[id];
+    if (p < n_tree) boxes[(n_tree - 1) + p] = prim_boxes[id];  // positions >= n_tree hold the hoisted primitives
     if (id < S) {
         int pos = sphere_pos[p];
         const SphereIn& s = sp[id];
@@ -195,6 +220,15 @@ inline size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
 
 }  // namespace
 
+static cudaError_t write_empty_root(void* d_nodes, cudaStream_t stream) {
+    float h[32];
+    for (int a = 0; a < 3; ++a)
+        for (int i = 0; i < 4; ++i) { h[a * 4 + i] = __builtin_huge_valf(); h[12 + a * 4 + i] = -__builtin_huge_valf(); }
+    int32_t* ch = reinterpret_cast<int32_t*>(h + 24);
+    for (int i = 0; i < 4; ++i) { ch[i] = lbvh::kEmpty; ch[4 + i] = 0; }
+    return cudaMemcpyAsync(d_nodes, h, 128, cudaMemcpyHostToDevice, stream);
+}
+
 #define BG_CUDA(expr)                     \
     do {                                  \
         cudaError_t e_ = (expr);          \
@@ -233,12 +267,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     r.bytes_prims = (size_t)(S ? S * 24 : 32) + (size_t)(P ? P * 80 : 16);
 
     if (n == 0) {  // empty scene: one node whose four slots fail every slab test
-        float h[32];
-        for (int a = 0; a < 3; ++a)
-            for (int i = 0; i < 4; ++i) { h[a * 4 + i] = __builtin_huge_valf(); h[12 + a * 4 + i] = -__builtin_huge_valf(); }
-        int32_t* ch = reinterpret_cast<int32_t*>(h + 24);
-        for (int i = 0; i < 4; ++i) { ch[i] = lbvh::kEmpty; ch[4 + i] = 0; }
-        BG_CUDA(cudaMemcpyAsync(r.d_nodes, h, 128, cudaMemcpyHostToDevice, stream));
+        BG_CUDA(write_empty_root(r.d_nodes, stream));
         BG_CUDA(cudaStreamSynchronize(stream));
         r.num_nodes = 1;
         r.depth = 1;
@@ -265,7 +294,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
                   8 * pad256((size_t)n * 4) +       // arrived, is_sphere, sphere_pos, leaf_refs, items x2, inner_cnt, inner_off
                   2 * pad256((size_t)n * 16) +      // kids, collapse tables
                   2 * pad256((size_t)max_nodes * 4) +  // dep, need
-                  pad256(sort_tmp) + pad256(scan_tmp) + 4 * 256;
+                  pad256(sort_tmp) + pad256(scan_tmp) + 6 * 256 + pad256(lbvh::kHoistCandCap * sizeof(int2));
     BG_CUDA(cudaMalloc((void**)&arena.base, need));
     arena.size = need;
     Box* prim_boxes = arena.take<Box>(n);
@@ -290,29 +319,72 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     int* need_s = arena.take<int>(max_nodes);
     void* d_sort_tmp = arena.take<char>(sort_tmp);
     void* d_scan_tmp = arena.take<char>(scan_tmp);
-    unsigned int* bounds6 = arena.take<unsigned int>(8);
+    unsigned int* bounds12 = arena.take<unsigned int>(12);
+    int* cand_count = arena.take<int>(1);
+    int2* cand = arena.take<int2>(lbvh::kHoistCandCap);
     int* next_count = arena.take<int>(1);
     double* sah = arena.take<double>(1);
 
     BG_CUDA(cudaStreamSynchronize(stream));
     auto t1 = std::chrono::steady_clock::now();
 
-    const unsigned int b6[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
-    BG_CUDA(cudaMemcpyAsync(bounds6, b6, sizeof b6, cudaMemcpyHostToDevice, stream));
+    const unsigned int b12[12] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    BG_CUDA(cudaMemcpyAsync(bounds12, b12, sizeof b12, cudaMemcpyHostToDevice, stream));
     BG_CUDA(cudaMemsetAsync(arrived, 0, (size_t)n * 4, stream));
     BG_CUDA(cudaMemsetAsync(sah, 0, 8, stream));
-    k_boxes<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, n, prim_boxes, bounds6);
-    k_keys<<<blocks_for(n), kThreads, 0, stream>>>(prim_boxes, n, bounds6, keys_a, vals_a);
+    BG_CUDA(cudaMemsetAsync(cand_count, 0, 4, stream));
+    k_boxes<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, n, prim_boxes, bounds12);
+
+    // hoisted primitives: the device lists the candidates, the host picks at most four (largest area first, then lowest
+    // index -- select_hoisted's rule in wide_bvh.cpp)
+    int hoist[4] = {-1, -1, -1, -1};
+    int nh = 0;
+    {
+        const char* e = getenv("RTB_HOIST");
+        if (!(e && atoi(e) == 0)) {
+            k_hoist<<<blocks_for(n), kThreads, 0, stream>>>(prim_boxes, n, bounds12, cand_count, cand);
+            int h_count = 0;
+            BG_CUDA(cudaMemcpyAsync(&h_count, cand_count, 4, cudaMemcpyDeviceToHost, stream));
+            BG_CUDA(cudaStreamSynchronize(stream));
+            if (h_count > 0 && h_count <= lbvh::kHoistCandCap) {
+                std::vector<int2> hc((size_t)h_count);
+                BG_CUDA(cudaMemcpy(hc.data(), cand, (size_t)h_count * sizeof(int2), cudaMemcpyDeviceToHost));
+                std::vector<std::pair<float, int>> byarea;
+                for (const int2& c : hc) {
+                    float a;
+                    memcpy(&a, &c.y, 4);
+                    byarea.emplace_back(-a, c.x);
+                }
+                std::sort(byarea.begin(), byarea.end());
+                for (size_t k = 0; k < byarea.size() && nh < lbvh::kMaxHoist; ++k) hoist[nh++] = byarea[k].second;
+            }
+        }
+    }
+    const int nt = n - nh;  // primitives in the tree
+    k_keys<<<blocks_for(n), kThreads, 0, stream>>>(prim_boxes, n, bounds12, make_int4(hoist[0], hoist[1], hoist[2], hoist[3]), keys_a, vals_a);
     BG_CUDA(cub::DeviceRadixSort::SortPairs(d_sort_tmp, sort_tmp, keys_a, keys_b, vals_a, vals_b, n, 0, 64, stream));
     k_flags<<<blocks_for(n), kThreads, 0, stream>>>(vals_b, n, S, is_sphere);
     BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, is_sphere, sphere_pos, n, stream));
-    k_pack<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, vals_b, sphere_pos, prim_boxes, n, boxes, leaf_refs,
+    k_pack<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, vals_b, sphere_pos, prim_boxes, n, nt, boxes, leaf_refs,
                                                   (float4*)r.d_spheres, (int2*)r.d_sphere_meta, (float4*)r.d_planes);
-    if (n > 1) {
-        k_radix<<<blocks_for(n - 1), kThreads, 0, stream>>>(keys_b, n, children, parent);
-        k_fit<<<blocks_for(n), kThreads, 0, stream>>>(children, parent, n, boxes, dp, arrived);
+    if (nt > 1) {
+        k_radix<<<blocks_for(nt - 1), kThreads, 0, stream>>>(keys_b, nt, children, parent);
+        k_fit<<<blocks_for(nt), kThreads, 0, stream>>>(children, parent, nt, boxes, dp, arrived);
     }
     BG_CUDA(cudaGetLastError());
+    r.num_hoisted = nh;
+    if (nh) BG_CUDA(cudaMemcpyAsync(r.hoisted, leaf_refs + nt, (size_t)nh * 4, cudaMemcpyDeviceToHost, stream));
+    if (nt == 0) {  // everything hoisted: the tree is one node whose slots fail every slab test
+        BG_CUDA(write_empty_root(r.d_nodes, stream));
+        BG_CUDA(cudaStreamSynchronize(stream));
+        r.num_nodes = 1;
+        r.depth = 1;
+        r.leaves = n;
+        cudaFree(arena.base);
+        if (d_sp) cudaFree(d_sp);
+        if (d_pl) cudaFree(d_pl);
+        return cudaSuccess;
+    }
 
     // breadth-first collapse; the host only learns each level's size (4 bytes per level)
     const char* pc = getenv("RTB_COST_PRIM");
@@ -327,9 +399,9 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
         if (base + count > max_nodes) { r.fail_line = __LINE__; BG_CUDA(cudaErrorUnknown); }
         level_base.push_back(base);
         level_count.push_back(count);
-        k_collapse_count<<<blocks_for(count), kThreads, 0, stream>>>(children, dp, n, cur, count, kids, inner_cnt);
+        k_collapse_count<<<blocks_for(count), kThreads, 0, stream>>>(children, dp, nt, cur, count, kids, inner_cnt);
         BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, inner_cnt, inner_off, count, stream));
-        k_collapse_write<<<blocks_for(count), kThreads, 0, stream>>>(boxes, leaf_refs, n, cur, kids, inner_off, inner_cnt, count, base,
+        k_collapse_write<<<blocks_for(count), kThreads, 0, stream>>>(boxes, leaf_refs, nt, cur, kids, inner_off, inner_cnt, count, base,
                                                                     (float*)r.d_nodes, nxt, next_count, prim_cost, sah);
         int h_next = 0;
         BG_CUDA(cudaMemcpyAsync(&h_next, next_count, 4, cudaMemcpyDeviceToHost, stream));

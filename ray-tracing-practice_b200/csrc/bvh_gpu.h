@@ -16,6 +16,8 @@ struct GpuBuildResult {
     void* d_planes = nullptr;       // 5 x float4 per plane
     size_t bytes_nodes = 0, bytes_prims = 0;
     int num_nodes = 0, depth = 0, max_stack = 0, leaves = 0, levels = 0;
+    int num_hoisted = 0;            // primitives kept out of the tree (wide_bvh.h), tested once per ray before the traversal
+    int hoisted[4] = {0, 0, 0, 0};  // their leaf references
     float sah_cost = 0.f;
     float upload_ms = 0.f;  // allocation + H2D of the caller's arrays
     float build_ms = 0.f;   // boxes, keys, sort, tree, fit, collapse, depth sweep (wall clock, stream idle on both sides)

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
 
     // per-lane state
     RayTrav rt;
-    trav_begin<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
+    trav_init<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
     rt.ref = kRefNeed;
     bool has_pixel = false;
     int px = 0, py = 0, sample = 0, chunk = 0;
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     rt.ref = kRefIdle;
                 }
             }
-            if (start_ray) trav_begin<X>(rt, ps.o, ps.d, 0.001f, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
+            if (start_ray) trav_begin<X, COUNT>(sc, rt, ps.o, ps.d, 0.001f, 1e30f, wc);  // Interval(0.001f, 1e30f), src/camera.cu:226
         }
         if (__all_sync(full, rt.ref == kRefIdle)) break;  // no pixels left for any lane
         // ================= TRACE phase: every lane runs its segment's closest-hit traversal to completion (traverse.cuh).

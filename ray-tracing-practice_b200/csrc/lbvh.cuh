@@ -90,6 +90,14 @@ LB_HD Box prim_box(const SphereIn* sp, int S, const PlaneIn* pl, int i) {
     return b;
 }
 
+// ---- step 1b: hoisted primitives (wide_bvh.h: the few whose box has >= kHoistAreaFraction of the scene box's area are
+// kept out of the tree and tested once per ray before the traversal).  Same rule as select_hoisted in wide_bvh.cpp.
+constexpr int kMaxHoist = 4;              // == kMaxHoisted
+constexpr float kHoistFraction = 0.25f;   // == kHoistAreaFraction
+constexpr int kHoistCandCap = 1024;       // candidates the device records; more than that (a scene made of scene-sized
+                                          // primitives) hoists nothing
+LB_HD bool hoist_candidate(const Box& b, float scene_area) { return scene_area > 0.f && box_area(b) >= LB_MUL(kHoistFraction, scene_area); }
+
 // floats as order-preserving unsigned keys, so scene bounds reduce with integer atomicMin/atomicMax
 LB_HD uint32_t float_to_ordered(float f) {
     union { float f; uint32_t u; } c;

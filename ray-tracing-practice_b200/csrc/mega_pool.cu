@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
     WorkCount wc = {0, 0, 0, 0, 0, 0};
 
     RayTrav rt;
-    trav_begin<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
+    trav_init<X>(rt, mk3(0, 0, 0), mk3(0, 0, 1), 0.001f, 1e30f);
     rt.ref = kRefIdle;
     int slot = 0;
 
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
             const int r = __popc(want & lt_mask);
             if (rt.ref == kRefIdle && r < n) {
                 slot = wp.in(kFReadyQ, (ws.ready_head + r) & (kPool - 1));
-                trav_begin<X>(rt, wp.ld3(kFOx, slot), wp.ld3(kFDx, slot), 0.001f, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
+                trav_begin<X, COUNT>(sc, rt, wp.ld3(kFOx, slot), wp.ld3(kFDx, slot), 0.001f, 1e30f, wc);  // Interval(0.001f, 1e30f), src/camera.cu:226
             }
             ws.ready_head = (ws.ready_head + n) & (kPool - 1);
             ws.ready_cnt -= n;

@@ -169,6 +169,8 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         total += g.bytes_nodes + g.bytes_prims;
         tree = {g.num_nodes, g.depth, g.max_stack, g.leaves, g.sah_cost, g.build_ms};
         gpu_upload_ms = g.upload_ms;
+        s->dev.num_hoisted = g.num_hoisted;
+        for (int k = 0; k < g.num_hoisted; ++k) s->dev.hoisted[k] = g.hoisted[k];
         PackedScene tmp = pack_scene(nullptr, 0, nullptr, 0, mt, M);  // material records only
         if ((rc = upload(&s->d_mats, tmp.mats.data(), tmp.mats.size() * sizeof(float), total))) return bail(rc);
     } else {
@@ -176,6 +178,8 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         PackedScene pk = pack_scene(sp, S, pl, P, mt, M);
         const WideBvh& bvh = pk.bvh;
         tree = {(int)bvh.nodes.size(), bvh.depth, bvh.max_stack, bvh.leaves, bvh.sah_cost, pk.build_ms};
+        s->dev.num_hoisted = (int)bvh.hoisted_refs.size();
+        for (int k = 0; k < s->dev.num_hoisted; ++k) s->dev.hoisted[k] = bvh.hoisted_refs[k];
         if ((rc = upload(&s->d_nodes, bvh.nodes.data(), bvh.nodes.size() * sizeof(WideNode), total))) return bail(rc);
         if ((rc = upload(&s->d_spheres, pk.spheres.data(), pk.spheres.size() * sizeof(float), total))) return bail(rc);
         if ((rc = upload(&s->d_sphere_meta, pk.sphere_meta.data(), pk.sphere_meta.size() * sizeof(int), total))) return bail(rc);

@@ -28,6 +28,8 @@ struct DevScene {
     int tex_w, tex_h, tex_mat;
     int num_nodes;
     int top_nodes;                           // wide nodes [0, top_nodes) are staged in shared memory
+    int num_hoisted;                         // primitives kept out of the tree (wide_bvh.h): tested once per ray in trav_begin
+    int hoisted[4];                          // their leaf references
 };
 
 #ifndef RTB_SMEM_STACK
@@ -38,6 +40,9 @@ struct DevScene {
 // the first design; measured on B200 it is 10 % SLOWER than all-local (two LDS/STS + address math + a shared/local branch
 // per push and pop, and it takes L1 capacity away from the nodes), so the default is 0.  The builder guarantees
 // max_stack <= 64.
+#ifndef RTB_FAST_SQRT
+#define RTB_FAST_SQRT 1
+#endif
 #ifndef RTB_SORT_PARTIAL
 #define RTB_SORT_PARTIAL 1
 #endif
@@ -58,6 +63,20 @@ struct WorkCount {
 };
 
 // ---- leaf tests ---------------------------------------------------------------------------------------------
+// sqrt of the discriminant: IEEE in exact mode (the reference's sqrtf, include/sphere.h:33); in fast mode the 2-instruction
+// approximation (2 ulp) instead of the ~10-instruction IEEE sequence -- measured 201.6 vs 203.1 ms on the headline frame
+template <bool X>
+__device__ __forceinline__ float leaf_sqrt(float D) {
+#if RTB_FAST_SQRT && defined(__CUDA_ARCH__)
+    if (!X) {
+        float s;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(D));
+        return s;
+    }
+#endif
+    return __fsqrt_rn(D);
+}
+
 // include/sphere.h:24-47.  a = |d|^2 and (fast mode) 1/a are per-ray constants.
 template <bool X>
 __device__ __forceinline__ bool sphere_t(V3 o, V3 d, float a, float inv_a, float4 s, float tmin, float tmax, float& t_out) {
@@ -66,7 +85,7 @@ __device__ __forceinline__ bool sphere_t(V3 o, V3 d, float a, float inv_a, float
     float cc = fsub<X>(len2_3<X>(oc), fmul<X>(s.w, s.w));
     float D = fsub<X>(fmul<X>(hb, hb), fmul<X>(a, cc));
     if (D < 0.0f) return false;
-    float sq = __fsqrt_rn(D);
+    float sq = leaf_sqrt<X>(D);
     float t;
     if (X) {
         t = (float)(((double)(-hb) - (double)sq) / (double)a);
@@ -167,7 +186,7 @@ struct TravStack {
 };
 
 template <bool X>
-__device__ __forceinline__ void trav_begin(RayTrav& r, V3 o, V3 d, float tmin, float tmax) {
+__device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, float tmax) {
     const float eps = 1e-20f;
     float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
     float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
@@ -328,6 +347,17 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
     trav_leaf<X, COUNT>(sc, r, wc, r.ref);
 }
 
+// Start of a segment: per-ray constants, then the hoisted primitives (the few that span most of the scene, kept out of the
+// tree by the builder).  Callers reach this point with the warp converged (the SHADE phase of the megakernel), so the floor
+// quad -- which most rays hit -- is tested at full lane occupancy instead of as a 2-lanes-active leaf step, and `closest`
+// already holds its hit when the traversal starts.  Exact mode: the update rule is the leaf step's, so the closest hit and
+// its tie-break do not depend on where a primitive is tested.
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trav_begin(const DevScene& sc, RayTrav& r, V3 o, V3 d, float tmin, float tmax, WorkCount& wc) {
+    trav_init<X>(r, o, d, tmin, tmax);
+    for (int k = 0; k < sc.num_hoisted; ++k) trav_leaf<X, COUNT>(sc, r, wc, sc.hoisted[k]);
+}
+
 // leaf step followed by the pop, with the top stack entry requested BEFORE the primitive test so that the two loads
 // (primitive, stack entry) are in flight together
 template <bool X, bool COUNT>
@@ -364,7 +394,7 @@ __device__ __forceinline__ void trace_closest(const DevScene& sc, const float4* 
     stk.st = s_st; stk.sr = s_sr; stk.lo = lstack;
     stk.tid = threadIdx.x; stk.nt = blockDim.x;
     RayTrav r;
-    trav_begin<X>(r, o, d, tmin, tmax);
+    trav_begin<X, COUNT>(sc, r, o, d, tmin, tmax, wc);
     while (r.ref != kRefDone) {
         bool pop = true;
         if (ref_is_leaf(r.ref)) trav_leaf<X, COUNT>(sc, r, wc);

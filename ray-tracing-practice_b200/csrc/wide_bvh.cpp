@@ -184,9 +184,47 @@ struct Builder {
 
 }  // namespace
 
-WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf) {
+// indices (into all_prims) of the primitives to hoist: box area >= kHoistAreaFraction of the scene box's, largest first
+static std::vector<int> select_hoisted(const std::vector<PrimBox>& all_prims) {
+    std::vector<int> pick;
+    if (const char* e = getenv("RTB_HOIST")) if (atoi(e) == 0) return pick;
+    Box3 scene;
+    scene.reset();
+    for (const PrimBox& p : all_prims) scene.grow(p.lo, p.hi);
+    const float sa = scene.area();
+    if (!(sa > 0.f)) return pick;
+    std::vector<std::pair<float, int>> cand;
+    for (size_t i = 0; i < all_prims.size(); ++i) {
+        Box3 b;
+        b.reset();
+        b.grow(all_prims[i].lo, all_prims[i].hi);
+        if (b.area() >= kHoistAreaFraction * sa) cand.emplace_back(-b.area(), (int)i);
+    }
+    std::sort(cand.begin(), cand.end());
+    for (size_t k = 0; k < cand.size() && (int)k < kMaxHoisted; ++k) pick.push_back(cand[k].second);
+    std::sort(pick.begin(), pick.end());
+    return pick;
+}
+
+WideBvh build_wide_bvh(const std::vector<PrimBox>& all_prims, int max_leaf) {
     WideBvh out;
     max_leaf = std::min(std::max(max_leaf, 1), 4);
+    const std::vector<int> hoist = select_hoisted(all_prims);
+    std::vector<PrimBox> prims;  // what the tree is built over
+    prims.reserve(all_prims.size());
+    for (size_t i = 0, h = 0; i < all_prims.size(); ++i) {
+        if (h < hoist.size() && hoist[h] == (int)i) { ++h; continue; }
+        prims.push_back(all_prims[i]);
+    }
+    // hoisted primitives take the slots after the tree's in the re-ordered arrays
+    auto append_hoisted = [&]() {
+        for (int i : hoist) {
+            const PrimBox& p = all_prims[i];
+            std::vector<int>& ord = p.type == 0 ? out.sphere_order : out.plane_order;
+            out.hoisted_refs.push_back(leaf_ref(p.type, (int)ord.size(), 1));
+            ord.push_back(p.index);
+        }
+    };
     if (prims.empty()) {
         WideNode root;
         for (int a = 0; a < 3; ++a)
@@ -194,6 +232,7 @@ WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf) {
         for (int i = 0; i < 4; ++i) { root.child[i] = kEmptyChild; root.pad[i] = 0; }
         out.nodes.push_back(root);
         out.depth = 1;
+        append_hoisted();
         return out;
     }
     Builder B(prims, max_leaf);
@@ -337,6 +376,7 @@ WideBvh build_wide_bvh(const std::vector<PrimBox>& prims, int max_leaf) {
     }
     out.depth = dep[0];
     out.max_stack = need[0];
+    append_hoisted();
     return out;
 }
 
@@ -426,6 +466,17 @@ int validate_wide_bvh(const WideBvh& bvh, const std::vector<PrimBox>& prims) {
             }
         }
     }
+    for (int32_t ch : bvh.hoisted_refs) {
+        uint32_t bits = (uint32_t)ch;
+        int type = (bits >> 30) & 1, cnt = ((bits >> 28) & 3) + 1, first = bits & 0x0fffffff;
+        const std::vector<int>& ord = type == 0 ? bvh.sphere_order : bvh.plane_order;
+        std::vector<char>& seen = type == 0 ? seen_s : seen_p;
+        if (ch >= 0 || cnt != 1 || (size_t)first >= ord.size()) return 11;
+        int orig = ord[first];
+        if (orig < 0 || (size_t)orig >= seen.size() || seen[orig]) return 12;
+        seen[orig] = 1;
+    }
+    if ((int)bvh.hoisted_refs.size() > kMaxHoisted) return 13;
     for (char s : seen_s) if (!s) return 10;
     for (char s : seen_p) if (!s) return 10;
     return 0;

@@ -25,6 +25,9 @@ struct alignas(128) WideNode {
 static_assert(sizeof(WideNode) == 128, "WideNode must be exactly one 128-byte line");
 
 constexpr int32_t kEmptyChild = 0x7fffffff;
+constexpr int kMaxHoisted = 4;
+// a primitive is hoisted when its box has at least this fraction of the scene box's surface area
+constexpr float kHoistAreaFraction = 0.25f;
 // leaf reference: bit31 set | type (1 bit, 0 sphere / 1 plane) | count-1 (2 bits) | first (28 bits)
 inline int32_t leaf_ref(int type, int first, int count) {
     return (int32_t)(0x80000000u | ((uint32_t)type << 30) | ((uint32_t)(count - 1) << 28) | (uint32_t)first);
@@ -45,6 +48,9 @@ struct WideBvh {
     int leaves = 0;
     float sah_cost = 0.f;
     int32_t root_ref = 0;           // 0 (inner root) or a leaf ref when the whole scene fits in one leaf
+    // Primitives that span most of the scene (the floor quad) are kept OUT of the tree: every ray tests them once, before
+    // the traversal, while the warp is still converged (traverse.cuh, trav_begin).  Leaf references, at most kMaxHoisted.
+    std::vector<int32_t> hoisted_refs;
 };
 
 struct SphereIn;

@@ -24,7 +24,7 @@ struct EmuScene {
 // one loop per kernel, a stable sort where the device uses cub's radix sort.  Replaces pk's tree and primitive streams.
 static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P, PackedScene& pk) {
     using lbvh::Box;
-    const int n = S + P;
+    int n = S + P;
     WideBvh& out = pk.bvh;
     out = WideBvh{};
     pk.spheres.assign((size_t)S * 4, 0.f);
@@ -51,9 +51,27 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
             cmax[a] = std::max(cmax[a], cc);
         }
     }
+    // k_hoist + the host's pick (bvh_gpu.cu)
+    int hoist[4] = {-1, -1, -1, -1}, nh = 0;
+    if (!(getenv("RTB_HOIST") && atoi(getenv("RTB_HOIST")) == 0)) {
+        Box sb = prim_boxes[0];
+        for (int i = 1; i < n; ++i) sb = lbvh::box_union(sb, prim_boxes[i]);
+        std::vector<std::pair<float, int>> byarea;
+        for (int i = 0; i < n; ++i)
+            if (lbvh::hoist_candidate(prim_boxes[i], lbvh::box_area(sb))) byarea.emplace_back(-lbvh::box_area(prim_boxes[i]), i);
+        if ((int)byarea.size() <= lbvh::kHoistCandCap) {
+            std::sort(byarea.begin(), byarea.end());
+            for (size_t k = 0; k < byarea.size() && nh < lbvh::kMaxHoist; ++k) hoist[nh++] = byarea[k].second;
+        }
+    }
+    const int n_all = n;
     std::vector<uint64_t> keys(n);
     std::vector<unsigned> vals(n);
-    for (int i = 0; i < n; ++i) { keys[i] = lbvh::morton_key(prim_boxes[i], cmin, cmax); vals[i] = (unsigned)i; }  // k_keys
+    for (int i = 0; i < n; ++i) {  // k_keys
+        const bool h = i == hoist[0] || i == hoist[1] || i == hoist[2] || i == hoist[3];
+        keys[i] = h ? ~0ull : lbvh::morton_key(prim_boxes[i], cmin, cmax);
+        vals[i] = (unsigned)i;
+    }
     std::stable_sort(vals.begin(), vals.end(), [&](unsigned a, unsigned b) { return keys[a] < keys[b]; });
     std::vector<uint64_t> skeys(n);
     for (int p = 0; p < n; ++p) skeys[p] = keys[vals[p]];
@@ -62,9 +80,10 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
     std::vector<Box> boxes(2 * (size_t)n);
     std::vector<int> leaf_refs(n);
     auto i2f = [](int v) { float f; memcpy(&f, &v, 4); return f; };
+    const int nt = n - nh;  // primitives in the tree; sorted positions >= nt hold the hoisted ones
     for (int p = 0; p < n; ++p) {  // k_pack
         int id = (int)vals[p];
-        boxes[(n - 1) + p] = prim_boxes[id];
+        if (p < nt) boxes[(nt - 1) + p] = prim_boxes[id];
         if (id < S) {
             int pos = sphere_pos[p];
             float* o = &pk.spheres[4 * (size_t)pos];
@@ -84,6 +103,25 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
             leaf_refs[p] = lbvh::make_leaf_ref(1, pos);
         }
     }
+    for (int k = 0; k < nh; ++k) out.hoisted_refs.push_back(leaf_refs[nt + k]);
+    auto finish_orders = [&]() {
+        out.leaves = n_all;
+        out.sphere_order.resize(S);
+        out.plane_order.resize(P);
+        for (int k = 0; k < S; ++k) out.sphere_order[k] = pk.sphere_meta[2 * (size_t)k + 1];
+        for (int k = 0; k < P; ++k) { int v; memcpy(&v, &pk.planes[20 * (size_t)k + 15], 4); out.plane_order[k] = v; }
+    };
+    if (nt == 0) {  // everything hoisted
+        WideNode root;
+        for (int a = 0; a < 3; ++a)
+            for (int i = 0; i < 4; ++i) { root.lo[a][i] = __builtin_huge_valf(); root.hi[a][i] = -__builtin_huge_valf(); }
+        for (int i = 0; i < 4; ++i) { root.child[i] = kEmptyChild; root.pad[i] = 0; }
+        out.nodes.push_back(root);
+        out.depth = 1;
+        finish_orders();
+        return;
+    }
+    n = nt;  // from here on: the tree
     std::vector<int2> children(n);
     std::vector<int> parent(2 * (size_t)n, -1);
     for (int i = 0; i < n - 1; ++i) {  // k_radix
@@ -136,11 +174,7 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
         }
     out.depth = dep[0];
     out.max_stack = need[0];
-    out.leaves = n;
-    out.sphere_order.resize(S);
-    out.plane_order.resize(P);
-    for (int k = 0; k < S; ++k) out.sphere_order[k] = pk.sphere_meta[2 * (size_t)k + 1];
-    for (int k = 0; k < P; ++k) { int v; memcpy(&v, &pk.planes[20 * (size_t)k + 15], 4); out.plane_order[k] = v; }
+    finish_orders();
 }
 
 extern "C" {
@@ -186,6 +220,8 @@ int emu_scene_create2(const void* sp, int S, const void* pl, int P, const void* 
     }
     s->dev.num_nodes = (int)s->pk.bvh.nodes.size();
     s->dev.top_nodes = 0;
+    s->dev.num_hoisted = (int)s->pk.bvh.hoisted_refs.size();
+    for (int k = 0; k < s->dev.num_hoisted; ++k) s->dev.hoisted[k] = s->pk.bvh.hoisted_refs[k];
     *out = s;
     return 0;
 }

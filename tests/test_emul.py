@@ -118,3 +118,40 @@ def test_lbvh_reference_stream_render_is_bit_identical(emul, EmuSceneCls):
     fb, cnt = es.render(g["camera"], rng=1, exact=1, tex_mode=0)
     assert cnt[0] == int(g["segments"][0])
     assert fb.tobytes() == g["fb_sum"].tobytes()
+
+
+# ---- hoisted primitives (wide_bvh.h): scene-spanning primitives are tested before the traversal, not through the tree
+
+def _big_planes_scene(rt, n_planes):
+    """n_planes stacked scene-sized quads (all hoist candidates) + a few small spheres between them"""
+    k = np.arange(n_planes, dtype=np.float32)
+    base = np.stack([np.full(n_planes, -10, np.float32), np.full(n_planes, -10, np.float32), -1.0 - k], 1)
+    u = np.tile(np.array([[20, 0, 0]], np.float32), (n_planes, 1))
+    v = np.tile(np.array([[0, 20, 0]], np.float32), (n_planes, 1))
+    pl = rt.make_planes(base, u, v, np.zeros(n_planes, np.int32), np.zeros(n_planes, np.int32))
+    sp = np.zeros(5, rt.SPHERE)
+    sp["center"] = [[0, 0, 0.5], [3, 1, 0.2], [-4, 2, 1.0], [1, -5, 0.3], [6, 6, 0.1]]
+    sp["radius"] = [0.5, 0.4, 0.7, 0.3, 0.6]
+    mt = np.zeros(1, rt.MATERIAL)
+    rng = np.random.default_rng(7)
+    rays = np.zeros((4000, 6), np.float32)
+    rays[:, :3] = rng.uniform(-8, 8, (4000, 3)) * [1, 1, 0] + [0, 0, 6]
+    rays[:, 3:] = rng.normal(size=(4000, 3)) * [0.6, 0.6, 0.2] + [0, 0, -1]
+    return sp, pl, mt, rays
+
+
+@pytest.mark.parametrize("n_planes,n_spheres", [(1, 0), (3, 5), (6, 5), (6, 0)])
+@pytest.mark.parametrize("builder", [0, 1])
+def test_hoisted_primitives_keep_the_closest_hit(emul, EmuSceneCls, orc, rt, n_planes, n_spheres, builder):
+    """all planes are hoist candidates: at most 4 leave the tree (largest first), the tree may even be empty; ids and t stay
+    those of the oracle's linear scan"""
+    sp, pl, mt, rays = _big_planes_scene(rt, n_planes)
+    sp = sp[:n_spheres]
+    es = EmuSceneCls(emul, sp, pl, mt, builder=builder)
+    ty, ix, t = es.trace(rays, exact=1)
+    oy, oi, orec = orc.scene(sp, pl, mt).trace(rays, 0)
+    assert (ty == oy).all() and (ix == oi).all()
+    hit = ty >= 0
+    assert hit.mean() > 0.5 and (bits(t[hit]) == bits(orec[hit, 0])).all()
+    out = np.zeros(4, np.int32)
+    assert emul.emu_lbvh_check(sp.ctypes.data if len(sp) else None, len(sp), pl.ctypes.data, len(pl), out.ctypes.data) == 0

@@ -121,3 +121,20 @@ def test_lbvh_build_is_deterministic_and_fast_at_full_size(rt):
     assert st["max_stack"] <= 64 and st["build_ms"] < 200.0
     a.close()
     b.close()
+
+
+@pytest.mark.parametrize("n_planes,n_spheres", [(1, 0), (3, 5), (6, 5), (6, 0)])
+@pytest.mark.parametrize("builder", [0, 1])
+def test_hoisted_primitives_keep_the_closest_hit(rt, orc, n_planes, n_spheres, builder):
+    """scene-sized quads are hoist candidates: at most 4 leave the tree (it may even end up empty) and are tested before the
+    traversal; ids and t stay those of the oracle's linear scan, with the host-built and the device-built tree"""
+    from test_emul import _big_planes_scene
+    sp, pl, mt, rays = _big_planes_scene(rt, n_planes)
+    sp = sp[:n_spheres]
+    sc = rt.Scene(sp, pl, mt, bvh_builder=builder)
+    ty, ix, t = sc.trace_primary(rays)
+    oy, oi, orec = orc.scene(sp, pl, mt).trace(rays, 0)
+    assert (ty == oy).all() and (ix == oi).all()
+    hit = ty >= 0
+    assert hit.mean() > 0.5 and (bits(t[hit]) == bits(orec[hit, 0])).all()
+    sc.close()

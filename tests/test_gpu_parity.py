@@ -249,7 +249,7 @@ def test_gpu_render_driver_distributes_frames(rt, tmp_path, monkeypatch):
     """frames of the camera path on several workers (RTB_GPUS; worker g -> device g % device_count): same files, log in frame order"""
     def run(tag, gpus):
         monkeypatch.setenv("RTB_GPUS", str(gpus))
-        hs = rt.HostScene(rt.test_config_text(W=64, H=40, sqrt_spp=2, max_depth=4, output=str(tmp_path / (tag + "_%d.bin")), num_frames=5), texture="")
+        hs = rt.HostScene(rt.shipped_config_text(W=64, H=40, sqrt_spp=2, max_depth=4, output=str(tmp_path / (tag + "_%d.bin")), num_frames=5), texture="")
         log = hs.gpu_render(0)
         return [l.split("\t")[0] for l in log.strip().split("\n")], [np.fromfile(tmp_path / ("%s_%d.bin" % (tag, n)), np.uint8) for n in range(5)]
     order1, files1 = run("a", 1)
