@@ -7,6 +7,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cub/block/block_scan.cuh>
 
 #include <algorithm>
 #include <chrono>
@@ -196,6 +197,54 @@ __global__ void k_collapse_write(const Box* __restrict__ boxes, const int* __res
     if ((threadIdx.x & 31) == 0 && cost != 0.f) atomicAdd(sah, (double)cost);
 }
 
+// ---- 6b. the first levels of the collapse (while a level has at most 1024 nodes) in ONE block: the same steps as the
+// count / scan / write launches above with a block scan in between, so the ~6 smallest levels cost one launch and one host
+// round trip instead of three launches and a round trip each.  Node order and contents are identical.
+constexpr int kTopThreads = 1024;
+constexpr int kTopMaxLevels = 24;
+struct TopLevels {
+    int base, count, nlevels;
+    int level_base[kTopMaxLevels], level_count[kTopMaxLevels];
+};
+__global__ void __launch_bounds__(kTopThreads) k_collapse_top(const int2* __restrict__ children, const lbvh::CollapseDp* __restrict__ dp,
+                                                               const Box* __restrict__ boxes, const int* __restrict__ leaf_refs, int n,
+                                                               int* items_a, int* items_b, float* nodes, float prim_cost, double* sah,
+                                                               TopLevels* out) {
+    typedef cub::BlockScan<int, kTopThreads> Scan;
+    __shared__ typename Scan::TempStorage scan_tmp;
+    int* cur = items_a;  // items_a[0] = 0 (the root) on entry; plain pointers: each level reads what the previous one wrote
+    int* nxt = items_b;
+    int base = 0, count = 1, lvl = 0;
+    const int k = threadIdx.x;
+    const float root_area = fmaxf(lbvh::box_area(boxes[0]), 1e-30f);
+    while (count > 0 && count <= kTopThreads && lvl < kTopMaxLevels) {
+        int kids[4] = {-1, -1, -1, -1};
+        int inner = 0, item = 0;
+        if (k < count) {
+            item = cur[k];
+            inner = lbvh::collapse_pick_dp(children, dp, n, item, kids);
+        }
+        int off = 0, total = 0;
+        Scan(scan_tmp).ExclusiveSum(inner, off, total);
+        float cost = 0.f;
+        if (k < count) {
+            lbvh::collapse_write(boxes, leaf_refs, n, kids, base + count, off, nodes + 32 * (size_t)(base + k), nxt);
+            cost = lbvh::box_area(boxes[n == 1 ? 0 : item]) / root_area;
+            for (int c = 0; c < 4; ++c)
+                if (kids[c] >= n - 1) cost += prim_cost * lbvh::box_area(boxes[kids[c]]) / root_area;
+        }
+        for (int o = 16; o > 0; o >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, o);
+        if ((k & 31) == 0 && cost != 0.f) atomicAdd(sah, (double)cost);
+        if (k == 0) { out->level_base[lvl] = base; out->level_count[lvl] = count; }
+        base += count;
+        count = total;
+        ++lvl;
+        int* t = cur; cur = nxt; nxt = t;
+        __syncthreads();  // the next level's items (global memory, written by this block) and scan_tmp are safe to reuse
+    }
+    if (k == 0) { out->base = base; out->count = count; out->nlevels = lvl; }
+}
+
 // ---- 7. depth / stack need of one level (children live in later levels, already final)
 __global__ void k_depth(const float* __restrict__ nodes, int base, int count, int* dep, int* need) {
     int k = blockIdx.x * blockDim.x + threadIdx.x;
@@ -294,7 +343,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
                   8 * pad256((size_t)n * 4) +       // arrived, is_sphere, sphere_pos, leaf_refs, items x2, inner_cnt, inner_off
                   2 * pad256((size_t)n * 16) +      // kids, collapse tables
                   2 * pad256((size_t)max_nodes * 4) +  // dep, need
-                  pad256(sort_tmp) + pad256(scan_tmp) + 6 * 256 + pad256(lbvh::kHoistCandCap * sizeof(int2));
+                  pad256(sort_tmp) + pad256(scan_tmp) + 6 * 256 + pad256(sizeof(TopLevels)) + pad256(lbvh::kHoistCandCap * sizeof(int2));
     BG_CUDA(cudaMalloc((void**)&arena.base, need));
     arena.size = need;
     Box* prim_boxes = arena.take<Box>(n);
@@ -323,6 +372,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     int* cand_count = arena.take<int>(1);
     int2* cand = arena.take<int2>(lbvh::kHoistCandCap);
     int* next_count = arena.take<int>(1);
+    TopLevels* top = arena.take<TopLevels>(1);
     double* sah = arena.take<double>(1);
 
     BG_CUDA(cudaStreamSynchronize(stream));
@@ -395,6 +445,16 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     int* cur = items_a;
     int* nxt = items_b;
     int base = 0, count = 1;
+    {   // the small top levels in one launch (k_collapse_top), one read-back
+        k_collapse_top<<<1, kTopThreads, 0, stream>>>(children, dp, boxes, leaf_refs, nt, items_a, items_b, (float*)r.d_nodes, prim_cost, sah, top);
+        TopLevels h_top;
+        BG_CUDA(cudaMemcpyAsync(&h_top, top, sizeof h_top, cudaMemcpyDeviceToHost, stream));
+        BG_CUDA(cudaStreamSynchronize(stream));
+        for (int l = 0; l < h_top.nlevels; ++l) { level_base.push_back(h_top.level_base[l]); level_count.push_back(h_top.level_count[l]); }
+        base = h_top.base;
+        count = h_top.count;
+        if (h_top.nlevels & 1) { cur = items_b; nxt = items_a; }
+    }
     while (count > 0) {
         if (base + count > max_nodes) { r.fail_line = __LINE__; BG_CUDA(cudaErrorUnknown); }
         level_base.push_back(base);

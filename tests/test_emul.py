@@ -155,3 +155,35 @@ def test_hoisted_primitives_keep_the_closest_hit(emul, EmuSceneCls, orc, rt, n_p
     assert hit.mean() > 0.5 and (bits(t[hit]) == bits(orec[hit, 0])).all()
     out = np.zeros(4, np.int32)
     assert emul.emu_lbvh_check(sp.ctypes.data if len(sp) else None, len(sp), pl.ctypes.data, len(pl), out.ctypes.data) == 0
+
+
+def _mixed_plane_scene(rt, n=300, seed=3):
+    """quads, ELLIPSES (never generated by create_scene, but part of PlaneData: include/plane.h:30-55) and triangles at
+    random orientations + spheres; rays from a sphere of origins towards the cloud"""
+    rng = np.random.default_rng(seed)
+    base = rng.uniform(-4, 4, (n, 3)).astype(np.float32)
+    u = rng.normal(size=(n, 3)).astype(np.float32)
+    v = np.cross(u, rng.normal(size=(n, 3))).astype(np.float32)
+    v *= (np.linalg.norm(u, axis=1) / np.maximum(np.linalg.norm(v, axis=1), 1e-6))[:, None].astype(np.float32)
+    pl = rt.make_planes(base, u, v, np.zeros(n, np.int32), (np.arange(n) % 3).astype(np.int32))
+    sp = np.zeros(50, rt.SPHERE)
+    sp["center"] = rng.uniform(-4, 4, (50, 3))
+    sp["radius"] = rng.uniform(0.1, 0.6, 50)
+    mt = np.zeros(1, rt.MATERIAL)
+    o = rng.normal(size=(6000, 3))
+    o = 9 * o / np.linalg.norm(o, axis=1)[:, None]
+    rays = np.concatenate([o, rng.uniform(-3, 3, (6000, 3)) - o], 1).astype(np.float32)
+    return sp, pl, mt, rays
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+def test_all_three_plane_types_match_the_oracle(emul, EmuSceneCls, orc, rt, builder):
+    sp, pl, mt, rays = _mixed_plane_scene(rt)
+    es = EmuSceneCls(emul, sp, pl, mt, builder=builder)
+    ty, ix, t = es.trace(rays, exact=1)
+    oy, oi, orec = orc.scene(sp, pl, mt).trace(rays, 0)
+    assert (ty == oy).all() and (ix == oi).all()
+    hit = ty >= 0
+    assert (bits(t[hit]) == bits(orec[hit, 0])).all()
+    for k in range(3):  # every plane type is actually hit
+        assert (pl["type"][ix[ty == 1]] == k).sum() > 50

@@ -138,3 +138,19 @@ def test_hoisted_primitives_keep_the_closest_hit(rt, orc, n_planes, n_spheres, b
     hit = ty >= 0
     assert hit.mean() > 0.5 and (bits(t[hit]) == bits(orec[hit, 0])).all()
     sc.close()
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+def test_all_three_plane_types_match_the_oracle(rt, orc, builder):
+    """quads, ellipses and triangles (include/plane.h:30-55) through both builders' trees: ids and t bits of the oracle's scan"""
+    from test_emul import _mixed_plane_scene
+    sp, pl, mt, rays = _mixed_plane_scene(rt)
+    sc = rt.Scene(sp, pl, mt, bvh_builder=builder)
+    ty, ix, t = sc.trace_primary(rays)
+    oy, oi, orec = orc.scene(sp, pl, mt).trace(rays, 0)
+    assert (ty == oy).all() and (ix == oi).all()
+    hit = ty >= 0
+    assert (bits(t[hit]) == bits(orec[hit, 0])).all()
+    for k in range(3):
+        assert (pl["type"][ix[ty == 1]] == k).sum() > 50
+    sc.close()
