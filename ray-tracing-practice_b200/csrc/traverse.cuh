@@ -40,6 +40,9 @@ struct DevScene {
 // the first design; measured on B200 it is 10 % SLOWER than all-local (two LDS/STS + address math + a shared/local branch
 // per push and pop, and it takes L1 capacity away from the nodes), so the default is 0.  The builder guarantees
 // max_stack <= 64.
+#ifndef RTB_FAST_SLAB
+#define RTB_FAST_SLAB 1
+#endif
 #ifndef RTB_FAST_SQRT
 #define RTB_FAST_SQRT 1
 #endif
@@ -260,7 +263,14 @@ __device__ __forceinline__ bool trav_inner(const DevScene& sc, const float4* __r
         float z0 = fmaf(nzs[i], r.idz, -r.ooz), z1 = fmaf(fzs[i], r.idz, -r.ooz);
         float tnear = fmaxf(fmaxf(x0, y0), fmaxf(z0, r.tmin));
         float tfar = fminf(fminf(x1, y1), fminf(z1, r.closest));
+#if RTB_FAST_SLAB
+        // fast mode: no widening of the far side.  The rounding of the slab products is ~6e-8 * (|origin| + |plane|) in world
+        // units, the leaf boxes are padded by >= 1e-4-ish (make_prim_boxes), and inner boxes are unions of them -- so only a
+        // ray that grazes a box edge AND the primitive inside within that rounding can be lost; exact mode keeps the guard.
+        bool h = X ? tnear <= fmaf(tfar, 1.0000005f, r.eps) : tnear <= tfar;
+#else
         bool h = tnear <= fmaf(tfar, 1.0000005f, r.eps);
+#endif
         tn[i] = h ? tnear : inf;
     }
     // sorting network on 4 (t, ref) pairs: (0,1)(2,3)(0,2)(1,3)(1,2)

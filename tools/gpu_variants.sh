@@ -8,9 +8,7 @@ run() { # name, lib, extra args
   echo "}" >> gpurun_out/variants.jsonl
 }
 D=ray-tracing-practice_b200/librt_b200.so
-run base $D ""
-run preload ray-tracing-practice_b200/build/preload.so ""
-run chunk1 $D "--chunk 1"
-run chunk4 $D "--chunk 4"
-run base2 $D ""
-run preload2 ray-tracing-practice_b200/build/preload.so ""
+for v in $VARIANTS; do
+  run base $D "$ARGS"
+  run $v ray-tracing-practice_b200/build/$v.so "$ARGS"
+done
