@@ -74,6 +74,8 @@ typedef struct rt_scene_stats {
     unsigned long long device_bytes;
     int bvh_builder;            /* RT_BVH_* the tree was built with */
     float input_upload_ms;      /* RT_BVH_GPU_LBVH: allocation + H2D of the caller's arrays (part of upload_ms) */
+    int num_hoisted;            /* primitives kept out of the tree because they span most of the scene (the floor quad):
+                                   tested once per ray before the traversal; at most 4 */
 } rt_scene_stats;
 
 /* Which builder replaces build_bvh (include/bvh_builder.h:99-120). */

@@ -253,6 +253,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
     s->stats.upload_ms = std::chrono::duration<float, std::milli>(t2 - t1).count() - tree.build_ms;
     s->stats.bvh_builder = builder;
     s->stats.input_upload_ms = gpu_upload_ms;
+    s->stats.num_hoisted = s->dev.num_hoisted;
     s->stats.device_bytes = total;
     *out = s;
     return RT_OK;

@@ -132,6 +132,7 @@ def test_hoisted_primitives_keep_the_closest_hit(rt, orc, n_planes, n_spheres, b
     sp, pl, mt, rays = _big_planes_scene(rt, n_planes)
     sp = sp[:n_spheres]
     sc = rt.Scene(sp, pl, mt, bvh_builder=builder)
+    assert sc.stats()["num_hoisted"] == min(n_planes, 4)
     ty, ix, t = sc.trace_primary(rays)
     oy, oi, orec = orc.scene(sp, pl, mt).trace(rays, 0)
     assert (ty == oy).all() and (ix == oi).all()
