@@ -187,3 +187,20 @@ def test_all_three_plane_types_match_the_oracle(emul, EmuSceneCls, orc, rt, buil
     assert (bits(t[hit]) == bits(orec[hit, 0])).all()
     for k in range(3):  # every plane type is actually hit
         assert (pl["type"][ix[ty == 1]] == k).sum() > 50
+
+
+def test_fast_mode_degrades_gracefully_with_camera_distance(emul, EmuSceneCls, rt):
+    """fast mode (fp32 leaf tests, unwidened slab test: traverse.cuh RTB_FAST_SLAB) loses precision with |origin| / scene size:
+    measured here so that the limit is known -- ids equal to exact mode's except on silhouette pixels at the scene's own camera
+    distance, a few per mille 10x further out, a few per cent 40x further out (exact mode keeps every guard)"""
+    hs = rt.synthetic_scene(2000, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    es = EmuSceneCls(emul, sp, pl, mt)
+    for dist, bound in ((15.0, 1e-3), (150.0, 6e-3), (600.0, 6e-2)):
+        cam = rt.build_camera(120, 160, [-dist, 0.3 * dist, 0.3 * dist], [0, 0, 0], 2 * np.degrees(np.arctan(12.0 / dist)), 1, 1)
+        rays = rt.pixel_center_rays(cam)
+        ty, ix, t = es.trace(rays, exact=1)
+        ty2, ix2, t2 = es.trace(rays, exact=0)
+        assert (ty >= 0).mean() > 0.3
+        mism = ((ty2 != ty) | (ix2 != ix)).mean()
+        assert mism < bound, (dist, mism)
