@@ -98,6 +98,11 @@ int rt_scene_create(const void* spheres, int num_spheres, const void* planes, in
 int rt_scene_create_ex(const void* spheres, int num_spheres, const void* planes, int num_planes, const void* materials,
                        int num_materials, const float* tex_rgba, int tex_w, int tex_h, int tex_material_idx,
                        const rt_scene_opts* opts, rt_scene** out);
+/* New geometry for an existing scene (materials and texture stay): rebuilds the tree and the SoA buffers with the DEVICE
+ * builder and swaps them in -- what an animated scene calls once per frame (the reference's scene is static; its build_bvh,
+ * include/bvh_builder.h:99, runs once).  Primitive counts may change; material indices must fit the scene's materials.
+ * On failure the scene keeps its previous geometry.  Not to be called while a rt_render_device frame is in flight. */
+int rt_scene_rebuild(rt_scene* scene, const void* spheres, int num_spheres, const void* planes, int num_planes);
 /* Replaces destroy_scene_arrays + destroy_all_materials (src/main.cu:310-344). */
 void rt_scene_destroy(rt_scene* scene);
 int rt_scene_get_stats(const rt_scene* scene, rt_scene_stats* out);

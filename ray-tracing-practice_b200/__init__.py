@@ -38,7 +38,7 @@ TEX_CPU, TEX_GPU = 0, 1
 BVH_HOST_SAH, BVH_GPU_LBVH = 0, 1
 TILE = 16
 
-C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
+C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_rebuild", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
                  "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
                  "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_set_device", "rt_version"]
 
@@ -92,6 +92,7 @@ def lib():
         L.rt_version.restype = C.c_char_p
         L.rt_scene_create.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp]
         L.rt_scene_create_ex.argtypes = [vp, ci, vp, ci, vp, ci, vp, ci, ci, ci, vp, vp]
+        L.rt_scene_rebuild.argtypes = [vp, vp, ci, vp, ci]
         L.rt_scene_destroy.argtypes = [vp]
         L.rt_scene_get_stats.argtypes = [vp, vp]
         L.rt_render.argtypes = [vp, vp, vp, vp, vp, vp, vp]
@@ -287,6 +288,12 @@ class Scene:
     def from_host(cls, host, bvh_builder=None):
         sp, pl, mt, tex = host.arrays()
         return cls(sp, pl, mt, tex, 0, bvh_builder=bvh_builder)
+
+    def rebuild(self, spheres, planes):
+        """rt_scene_rebuild: new geometry, device BVH build, same materials / texture"""
+        sp = np.ascontiguousarray(spheres, SPHERE)
+        pl = np.ascontiguousarray(planes, PLANE)
+        _check(lib().rt_scene_rebuild(self.h, _ptr(sp), len(sp), _ptr(pl), len(pl)))
 
     def stats(self):
         s = SceneStats()

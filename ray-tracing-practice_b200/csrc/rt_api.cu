@@ -259,6 +259,63 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
     return RT_OK;
 }
 
+int rt_scene_rebuild(rt_scene* s, const void* spheres, int S, const void* planes, int P) {
+    if (!s) return fail(RT_ERR_INVALID, "rt_scene_rebuild: scene is NULL");
+    if (S < 0 || P < 0 || (S && !spheres) || (P && !planes)) return fail(RT_ERR_INVALID, "rt_scene_rebuild: bad array");
+    if ((long long)S >= (1 << 28) || (long long)P >= (1 << 28)) return fail(RT_ERR_INVALID, "rt_scene_rebuild: too many primitives");
+    const SphereIn* sp = (const SphereIn*)spheres;
+    const PlaneIn* pl = (const PlaneIn*)planes;
+    const int M = s->stats.num_materials;
+    for (int i = 0; i < S; ++i)
+        if (sp[i].mat < 0 || sp[i].mat >= M) return fail(RT_ERR_INVALID, "rt_scene_rebuild: sphere material_idx out of range");
+    for (int i = 0; i < P; ++i) {
+        if (pl[i].mat < 0 || pl[i].mat >= M) return fail(RT_ERR_INVALID, "rt_scene_rebuild: plane material_idx out of range");
+        if (pl[i].type < 0 || pl[i].type > 2) return fail(RT_ERR_INVALID, "rt_scene_rebuild: plane type must be QUAD/ELLIPSE/TRIANGLE");
+    }
+    if (s->pending) return fail(RT_ERR_INVALID, "rt_scene_rebuild: a frame is in flight (call rt_render_finish first)");
+    RT_CUDA(cudaStreamSynchronize(s->stream));
+    GpuBuildResult g;
+    cudaError_t ge = gpu_build_scene(sp, S, pl, P, nullptr, g);
+    if (ge != cudaSuccess) {
+        cudaGetLastError();
+        char b[256];
+        snprintf(b, sizeof b, "CUDA error = %u (%s) in the device BVH build (bvh_gpu.cu:%d)", (unsigned)ge, cudaGetErrorString(ge), g.fail_line);
+        return fail(RT_ERR_CUDA, b);  // the scene keeps its previous geometry
+    }
+    if (g.max_stack > kSmemStack + kLocalStack) {
+        gpu_build_free(g);
+        return fail(RT_ERR_UNSUPPORTED, "rt_scene_rebuild: BVH needs a deeper traversal stack than the kernels provide");
+    }
+    void* old[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes};
+    for (void* b : old)
+        if (b) cudaFree(b);
+    s->d_nodes = g.d_nodes;
+    s->d_spheres = g.d_spheres;
+    s->d_sphere_meta = g.d_sphere_meta;
+    s->d_planes = g.d_planes;
+    s->dev.nodes = (const float4*)s->d_nodes;
+    s->dev.spheres = (const float4*)s->d_spheres;
+    s->dev.sphere_meta = (const int2*)s->d_sphere_meta;
+    s->dev.planes = (const float4*)s->d_planes;
+    s->dev.num_nodes = g.num_nodes;
+    s->default_top = g.num_nodes < 64 ? g.num_nodes : 64;
+    s->dev.top_nodes = s->default_top;
+    s->dev.num_hoisted = g.num_hoisted;
+    for (int k = 0; k < g.num_hoisted; ++k) s->dev.hoisted[k] = g.hoisted[k];
+    s->stats.num_spheres = S;
+    s->stats.num_planes = P;
+    s->stats.wide_nodes = g.num_nodes;
+    s->stats.wide_depth = g.depth;
+    s->stats.max_stack = g.max_stack;
+    s->stats.leaves = g.leaves;
+    s->stats.sah_cost = g.sah_cost;
+    s->stats.build_ms = g.build_ms;
+    s->stats.input_upload_ms = g.upload_ms;
+    s->stats.bvh_builder = RT_BVH_GPU_LBVH;
+    s->stats.num_hoisted = g.num_hoisted;
+    return RT_OK;
+}
+
 void rt_scene_destroy(rt_scene* s) {
     if (!s) return;
     if (s->stream) cudaStreamSynchronize(s->stream);

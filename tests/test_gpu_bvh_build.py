@@ -155,3 +155,40 @@ def test_all_three_plane_types_match_the_oracle(rt, orc, builder):
     for k in range(3):
         assert (pl["type"][ix[ty == 1]] == k).sum() > 50
     sc.close()
+
+
+def test_scene_rebuild_swaps_geometry_in_place(rt, orc):
+    """rt_scene_rebuild: an animated scene re-submits its primitives each frame; hits follow the new geometry (oracle scan),
+    counts may change, materials stay, and a frame rendered after the rebuild equals a freshly created scene's"""
+    hs = rt.synthetic_scene(3000, W=96, H=54, sqrt_spp=2, depth=6, seed=21)
+    sp, pl, mt, _ = hs.arrays()
+    sc = rt.Scene(sp, pl, mt)
+    cam = rt.build_camera(135, 240, [-15, 0, 4.5], [0, 0, 4.5], 90.0, 1, 1)
+    rays = rt.pixel_center_rays(cam)
+    before = sc.trace_primary(rays)
+    for step in range(3):
+        moved = sp.copy()
+        moved["center"][:, 2] += 0.15 * (step + 1) * np.sin(np.arange(len(sp)))[:, None].ravel()
+        moved = moved[: len(sp) - 500 * step]
+        sc.rebuild(moved, pl)
+        st = sc.stats()
+        assert st["num_spheres"] == len(moved) and st["bvh_builder"] == rt.BVH_GPU_LBVH and st["max_stack"] <= 64
+        ty, ix, t = sc.trace_primary(rays)
+        sel = np.arange(0, len(rays), 53)
+        oy, oi, orec = orc.scene(moved, pl, mt).trace(rays[sel], 0)
+        assert (ty[sel] == oy).all() and (ix[sel] == oi).all()
+        hit = oy >= 0
+        assert (bits(t[sel][hit]) == bits(orec[hit, 0])).all()
+        fresh = rt.Scene(moved, pl, mt, bvh_builder=rt.BVH_GPU_LBVH)
+        fa, ia = sc.render(hs.camera(0), rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+        fb, ib = fresh.render(hs.camera(0), rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+        assert fa.tobytes() == fb.tobytes() and ia["segments"] == ib["segments"]
+        fresh.close()
+    assert ((sc.trace_primary(rays)[1] != before[1]).mean()) > 0.01  # the geometry did change
+    bad = sp.copy()
+    bad["material_idx"][0] = 10 ** 6
+    with pytest.raises(rt.RtError):
+        sc.rebuild(bad, pl)
+    ty2, ix2, _ = sc.trace_primary(rays)  # a refused rebuild leaves the scene as it was
+    assert (ty2 == ty).all() and (ix2 == ix).all()
+    sc.close()
