@@ -97,7 +97,7 @@ __global__ void k_flags(const unsigned int* __restrict__ vals, int n, int S, int
 __global__ void k_pack(const SphereIn* __restrict__ sp, int S, const PlaneIn* __restrict__ pl, const unsigned int* __restrict__ vals,
                        const int* __restrict__ sphere_pos, const Box* __restrict__ prim_boxes, int n, int n_tree, Box* __restrict__ boxes,
                        int* __restrict__ leaf_refs, float4* __restrict__ spheres, int2* __restrict__ sphere_meta,
-                       float4* __restrict__ planes) {
+                       float4* __restrict__ planes, float4* __restrict__ planes_fast) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int id = (int)vals[p];
@@ -117,6 +117,12 @@ __global__ void k_pack(const SphereIn* __restrict__ sp, int S, const PlaneIn* __
         o[2] = make_float4(q.u[0], q.u[1], q.u[2], __int_as_float(q.mat));
         o[3] = make_float4(q.v[0], q.v[1], q.v[2], __int_as_float(id - S));
         o[4] = make_float4(q.base[0], q.base[1], q.base[2], 0.f);
+        float f[12];
+        lbvh::plane_fast_record(q, f);
+        float4* of = planes_fast + 3 * (size_t)pos;
+        of[0] = make_float4(f[0], f[1], f[2], f[3]);
+        of[1] = make_float4(f[4], f[5], f[6], f[7]);
+        of[2] = make_float4(f[8], f[9], f[10], f[11]);
         leaf_refs[p] = lbvh::make_leaf_ref(1, pos);
     }
 }
@@ -292,10 +298,10 @@ static cudaError_t write_empty_root(void* d_nodes, cudaStream_t stream) {
     } while (0)
 
 void gpu_build_free(GpuBuildResult& r) {
-    void* bufs[] = {r.d_nodes, r.d_spheres, r.d_sphere_meta, r.d_planes};
+    void* bufs[] = {r.d_nodes, r.d_spheres, r.d_sphere_meta, r.d_planes, r.d_planes_fast};
     for (void* b : bufs)
         if (b) cudaFree(b);
-    r.d_nodes = r.d_spheres = r.d_sphere_meta = r.d_planes = nullptr;
+    r.d_nodes = r.d_spheres = r.d_sphere_meta = r.d_planes = r.d_planes_fast = nullptr;
 }
 
 cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, int P, cudaStream_t stream, GpuBuildResult& r) {
@@ -312,8 +318,9 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     BG_CUDA(cudaMalloc(&r.d_spheres, S ? (size_t)S * 16 : 16));
     BG_CUDA(cudaMalloc(&r.d_sphere_meta, S ? (size_t)S * 8 : 16));
     BG_CUDA(cudaMalloc(&r.d_planes, P ? (size_t)P * 80 : 16));
+    BG_CUDA(cudaMalloc(&r.d_planes_fast, P ? (size_t)P * 48 : 16));
     r.bytes_nodes = (size_t)max_nodes * 128;
-    r.bytes_prims = (size_t)(S ? S * 24 : 32) + (size_t)(P ? P * 80 : 16);
+    r.bytes_prims = (size_t)(S ? S * 24 : 32) + (size_t)(P ? P * 128 : 32);
 
     if (n == 0) {  // empty scene: one node whose four slots fail every slab test
         BG_CUDA(write_empty_root(r.d_nodes, stream));
@@ -416,7 +423,7 @@ cudaError_t gpu_build_scene(const SphereIn* h_sp, int S, const PlaneIn* h_pl, in
     k_flags<<<blocks_for(n), kThreads, 0, stream>>>(vals_b, n, S, is_sphere);
     BG_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp, is_sphere, sphere_pos, n, stream));
     k_pack<<<blocks_for(n), kThreads, 0, stream>>>(d_sp, S, d_pl, vals_b, sphere_pos, prim_boxes, n, nt, boxes, leaf_refs,
-                                                  (float4*)r.d_spheres, (int2*)r.d_sphere_meta, (float4*)r.d_planes);
+                                                  (float4*)r.d_spheres, (int2*)r.d_sphere_meta, (float4*)r.d_planes, (float4*)r.d_planes_fast);
     if (nt > 1) {
         k_radix<<<blocks_for(nt - 1), kThreads, 0, stream>>>(keys_b, nt, children, parent);
         k_fit<<<blocks_for(nt), kThreads, 0, stream>>>(children, parent, nt, boxes, dp, arrived);

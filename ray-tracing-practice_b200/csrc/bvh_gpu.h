@@ -14,6 +14,7 @@ struct GpuBuildResult {
     void* d_spheres = nullptr;      // float4 (cx,cy,cz,r), leaf (Morton) order
     void* d_sphere_meta = nullptr;  // int2 (material, caller's index)
     void* d_planes = nullptr;       // 5 x float4 per plane
+    void* d_planes_fast = nullptr;  // 3 x float4 per plane: the fast-mode record (lbvh.cuh, plane_fast_record)
     size_t bytes_nodes = 0, bytes_prims = 0;
     int num_nodes = 0, depth = 0, max_stack = 0, leaves = 0, levels = 0;
     int num_hoisted = 0;            // primitives kept out of the tree (wide_bvh.h), tested once per ray before the traversal

@@ -98,6 +98,31 @@ constexpr int kHoistCandCap = 1024;       // candidates the device records; more
                                           // primitives) hoists nothing
 LB_HD bool hoist_candidate(const Box& b, float scene_area) { return scene_area > 0.f && box_area(b) >= LB_MUL(kHoistFraction, scene_area); }
 
+// ---- fast-mode plane record (traverse.cuh, plane_fast_t): 12 floats = 3 x float4 per plane,
+//     (n, D)  (A, a0)  (B, b0)   with  A = v x w,  a0 = A . base,  B = w x u,  b0 = B . base,
+// so that the reference's interior coordinates (include/plane.h:73-76: alpha = w . ((p - base) x v), beta = w . (u x (p - base)))
+// become alpha = A . p - a0, beta = B . p - b0 -- two dot products instead of two cross products and two dot products.
+// The plane type (0 quad, 1 ellipse, 2 triangle) rides in the two lowest mantissa bits of a0 (moves the alpha = 0 edge
+// by < 3 ulp of a0).  Only the production (fast-math) traversal reads these; exact mode keeps the reference's arithmetic.
+LB_HD void plane_fast_record(const PlaneIn& p, float out[12]) {
+    // separately rounded products (LB_*): the host packer and the device packer produce the same bits
+    float A[3], B[3];
+    for (int i = 0; i < 3; ++i) {
+        const int j = (i + 1) % 3, k = (i + 2) % 3;
+        A[i] = LB_SUB(LB_MUL(p.v[j], p.w[k]), LB_MUL(p.v[k], p.w[j]));
+        B[i] = LB_SUB(LB_MUL(p.w[j], p.u[k]), LB_MUL(p.w[k], p.u[j]));
+    }
+    float a0 = LB_ADD(LB_ADD(LB_MUL(A[0], p.base[0]), LB_MUL(A[1], p.base[1])), LB_MUL(A[2], p.base[2]));
+    const float b0 = LB_ADD(LB_ADD(LB_MUL(B[0], p.base[0]), LB_MUL(B[1], p.base[1])), LB_MUL(B[2], p.base[2]));
+    union { float f; uint32_t u; } c;
+    c.f = a0;
+    c.u = (c.u & ~3u) | ((uint32_t)p.type & 3u);
+    a0 = c.f;
+    out[0] = p.n[0]; out[1] = p.n[1]; out[2] = p.n[2]; out[3] = p.D;
+    out[4] = A[0]; out[5] = A[1]; out[6] = A[2]; out[7] = a0;
+    out[8] = B[0]; out[9] = B[1]; out[10] = B[2]; out[11] = b0;
+}
+
 // floats as order-preserving unsigned keys, so scene bounds reduce with integer atomicMin/atomicMax
 LB_HD uint32_t float_to_ordered(float f) {
     union { float f; uint32_t u; } c;

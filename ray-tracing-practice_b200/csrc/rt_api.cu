@@ -55,6 +55,7 @@ struct rt_scene {
     void* d_spheres = nullptr;
     void* d_sphere_meta = nullptr;
     void* d_planes = nullptr;
+    void* d_planes_fast = nullptr;
     void* d_mats = nullptr;
     void* d_tex = nullptr;
     cudaArray_t tex_array = nullptr;
@@ -166,6 +167,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         s->d_spheres = g.d_spheres;
         s->d_sphere_meta = g.d_sphere_meta;
         s->d_planes = g.d_planes;
+        s->d_planes_fast = g.d_planes_fast;
         total += g.bytes_nodes + g.bytes_prims;
         tree = {g.num_nodes, g.depth, g.max_stack, g.leaves, g.sah_cost, g.build_ms};
         gpu_upload_ms = g.upload_ms;
@@ -184,6 +186,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         if ((rc = upload(&s->d_spheres, pk.spheres.data(), pk.spheres.size() * sizeof(float), total))) return bail(rc);
         if ((rc = upload(&s->d_sphere_meta, pk.sphere_meta.data(), pk.sphere_meta.size() * sizeof(int), total))) return bail(rc);
         if ((rc = upload(&s->d_planes, pk.planes.data(), pk.planes.size() * sizeof(float), total))) return bail(rc);
+        if ((rc = upload(&s->d_planes_fast, pk.planes_fast.data(), pk.planes_fast.size() * sizeof(float), total))) return bail(rc);
         if ((rc = upload(&s->d_mats, pk.mats.data(), pk.mats.size() * sizeof(float), total))) return bail(rc);
     }
     if (tree.max_stack > kSmemStack + kLocalStack) {
@@ -233,6 +236,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
     s->dev.spheres = (const float4*)s->d_spheres;
     s->dev.sphere_meta = (const int2*)s->d_sphere_meta;
     s->dev.planes = (const float4*)s->d_planes;
+    s->dev.planes_fast = (const float4*)s->d_planes_fast;
     s->dev.mats = (const float4*)s->d_mats;
     s->dev.tex = (const float4*)s->d_tex;
     s->dev.tex_obj = s->tex_obj;
@@ -286,13 +290,15 @@ int rt_scene_rebuild(rt_scene* s, const void* spheres, int S, const void* planes
         gpu_build_free(g);
         return fail(RT_ERR_UNSUPPORTED, "rt_scene_rebuild: BVH needs a deeper traversal stack than the kernels provide");
     }
-    void* old[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes};
+    void* old[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast};
     for (void* b : old)
         if (b) cudaFree(b);
     s->d_nodes = g.d_nodes;
     s->d_spheres = g.d_spheres;
     s->d_sphere_meta = g.d_sphere_meta;
     s->d_planes = g.d_planes;
+    s->d_planes_fast = g.d_planes_fast;
+    s->dev.planes_fast = (const float4*)s->d_planes_fast;
     s->dev.nodes = (const float4*)s->d_nodes;
     s->dev.spheres = (const float4*)s->d_spheres;
     s->dev.sphere_meta = (const int2*)s->d_sphere_meta;
@@ -321,7 +327,7 @@ void rt_scene_destroy(rt_scene* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
     if (s->tex_array) cudaFreeArray(s->tex_array);
-    void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
+    void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
                     s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_part};
     for (void* b : bufs)
         if (b) cudaFree(b);

@@ -1,5 +1,7 @@
 #include "scene_pack.h"
 
+#include "lbvh.cuh"
+
 #include <chrono>
 #include <cstring>
 
@@ -25,6 +27,7 @@ PackedScene pack_scene(const SphereIn* sp, int S, const PlaneIn* pl, int P, cons
         ps.sphere_meta[2 * k + 1] = bvh.sphere_order[k];
     }
     ps.planes.resize(bvh.plane_order.size() * 20);
+    ps.planes_fast.resize(bvh.plane_order.size() * 12);
     for (size_t k = 0; k < bvh.plane_order.size(); ++k) {
         const PlaneIn& p = pl[bvh.plane_order[k]];
         float* o = &ps.planes[20 * k];
@@ -33,6 +36,7 @@ PackedScene pack_scene(const SphereIn* sp, int S, const PlaneIn* pl, int P, cons
         o[8] = p.u[0]; o[9] = p.u[1]; o[10] = p.u[2]; o[11] = i2f(p.mat);
         o[12] = p.v[0]; o[13] = p.v[1]; o[14] = p.v[2]; o[15] = i2f(bvh.plane_order[k]);
         o[16] = p.base[0]; o[17] = p.base[1]; o[18] = p.base[2]; o[19] = 0.f;
+        lbvh::plane_fast_record(p, &ps.planes_fast[12 * k]);
     }
     ps.mats.resize((size_t)M * 12);
     for (int i = 0; i < M; ++i) {

@@ -14,6 +14,7 @@ struct PackedScene {
     std::vector<float> spheres;      // 4 per sphere: cx,cy,cz,r                      (leaf order)
     std::vector<int> sphere_meta;    // 2 per sphere: material_idx, caller's index
     std::vector<float> planes;       // 20 per plane: (n,D) (w,type) (u,mat) (v,caller's index) (base,0)
+    std::vector<float> planes_fast;  // 12 per plane: the fast-mode record of lbvh.cuh (plane_fast_record), same order
     std::vector<float> mats;         // 12 per material: (albedo,type) (emit,fuzz) (absorption,ir)
     float build_ms = 0.f;
 };

@@ -30,6 +30,7 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
     pk.spheres.assign((size_t)S * 4, 0.f);
     pk.sphere_meta.assign((size_t)S * 2, 0);
     pk.planes.assign((size_t)P * 20, 0.f);
+    pk.planes_fast.assign((size_t)P * 12, 0.f);
     if (n == 0) {
         WideNode root;
         for (int a = 0; a < 3; ++a)
@@ -100,6 +101,7 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
             o[8] = q.u[0]; o[9] = q.u[1]; o[10] = q.u[2]; o[11] = i2f(q.mat);
             o[12] = q.v[0]; o[13] = q.v[1]; o[14] = q.v[2]; o[15] = i2f(id - S);
             o[16] = q.base[0]; o[17] = q.base[1]; o[18] = q.base[2]; o[19] = 0.f;
+            lbvh::plane_fast_record(q, &pk.planes_fast[12 * (size_t)pos]);
             leaf_refs[p] = lbvh::make_leaf_ref(1, pos);
         }
     }
@@ -211,6 +213,7 @@ int emu_scene_create2(const void* sp, int S, const void* pl, int P, const void* 
     s->dev.spheres = (const float4*)s->pk.spheres.data();
     s->dev.sphere_meta = (const int2*)s->pk.sphere_meta.data();
     s->dev.planes = (const float4*)s->pk.planes.data();
+    s->dev.planes_fast = (const float4*)s->pk.planes_fast.data();
     s->dev.mats = (const float4*)s->pk.mats.data();
     s->dev.tex_mat = -1;
     if (tex) {

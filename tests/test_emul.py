@@ -204,3 +204,19 @@ def test_fast_mode_degrades_gracefully_with_camera_distance(emul, EmuSceneCls, r
         assert (ty >= 0).mean() > 0.3
         mism = ((ty2 != ty) | (ix2 != ix)).mean()
         assert mism < bound, (dist, mism)
+
+
+@pytest.mark.parametrize("builder", [0, 1])
+def test_fast_plane_record_agrees_with_the_reference_arithmetic(emul, EmuSceneCls, rt, builder):
+    """fast mode tests planes on the 3 x float4 record (alpha = A.p - a0, type in a0's low mantissa bits; lbvh.cuh): same hits
+    as the reference's cross-product form except rays within fp32 noise of a plane's edge, for quads, ellipses and triangles"""
+    sp, pl, mt, rays = _mixed_plane_scene(rt)
+    es = EmuSceneCls(emul, sp[:0], pl, mt, builder=builder)   # planes only
+    ty, ix, t = es.trace(rays, exact=1)
+    ty2, ix2, t2 = es.trace(rays, exact=0)
+    assert (ty >= 0).mean() > 0.5
+    assert ((ty2 != ty) | (ix2 != ix)).mean() < 2e-3
+    same = (ty >= 0) & (ty2 == ty) & (ix2 == ix)
+    assert np.max(np.abs(t2[same] - t[same]) / t[same]) < 1e-4
+    for k in range(3):
+        assert (pl["type"][ix2[ty2 == 1]] == k).sum() > 50

@@ -26,9 +26,16 @@ def main():
     ap.add_argument("--builder", default="host", choices=["host", "gpu"], help="BVH builder: host binned SAH / device LBVH")
     ap.add_argument("--chunk", type=int, default=0, help="sample_chunk option (0 auto, -1 whole pixels)")
     a = ap.parse_args()
-    cfg = rt.CONFIGS[a.workload]
-    hs = rt.synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
-    scene = rt.Scene.from_host(hs, bvh_builder=rt.BVH_GPU_LBVH if a.builder == "gpu" else rt.BVH_HOST_SAH)
+    builder = rt.BVH_GPU_LBVH if a.builder == "gpu" else rt.BVH_HOST_SAH
+    if a.workload == "shipped":  # BASELINE configs[0]: the reference's own config.txt scene (synthetic stand-in for floor.jpg)
+        cfg = dict(W=1080, H=720)
+        hs = rt.HostScene(rt.shipped_config_text(), texture="")
+        sp, pl, mt, _ = hs.arrays()
+        scene = rt.Scene(sp, pl, mt, rt.synthetic_texture(), 0, bvh_builder=builder)
+    else:
+        cfg = rt.CONFIGS[a.workload]
+        hs = rt.synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
+        scene = rt.Scene.from_host(hs, bvh_builder=builder)
     cam = hs.camera(a.frame)
     if a.spp:
         cam["samples_per_pixel"] = a.spp
