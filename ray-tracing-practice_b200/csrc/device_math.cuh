@@ -36,13 +36,51 @@ template <bool X> __device__ __forceinline__ V3 cross3(V3 a, V3 b) {
     return mk3(fsub<X>(fmul<X>(a.y, b.z), fmul<X>(a.z, b.y)), fsub<X>(fmul<X>(a.z, b.x), fmul<X>(a.x, b.z)),
                fsub<X>(fmul<X>(a.x, b.y), fmul<X>(a.y, b.x)));
 }
+// Fast-mode (production) special functions: the SFU approximations (1-2 ulp, 2 instructions) instead of the IEEE-rounded
+// sequences with their slow-path calls.  Exact mode never uses them.  RTB_FAST_SFU=0 restores the IEEE versions.
+#ifndef RTB_FAST_SFU
+#define RTB_FAST_SFU 1
+#endif
+__device__ __forceinline__ float fast_sqrt(float x) {
+#if RTB_FAST_SFU && defined(__CUDA_ARCH__)
+    float s;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(x));
+    return s;
+#else
+    return sqrtf(x);
+#endif
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+#if RTB_FAST_SFU && defined(__CUDA_ARCH__)
+    return __fdividef(1.0f, x);
+#else
+    return __frcp_rn(x);
+#endif
+}
+__device__ __forceinline__ float fast_cbrt01(float u) {  // u in [0, 1]
+#if RTB_FAST_SFU && defined(__CUDA_ARCH__)
+    return exp2f(__log2f(u) * (1.0f / 3.0f));  // MUFU.LG2, FMUL, MUFU.EX2; u = 0 -> 0
+#else
+    return cbrtf(u);
+#endif
+}
+__device__ __forceinline__ void fast_sincos2pi(float u, float* sn, float* cs) {  // sin / cos of 2*pi*u, u in [0, 1)
+#ifndef RTB_FAST_SINCOS
+#define RTB_FAST_SINCOS 1
+#endif
+#if RTB_FAST_SFU && RTB_FAST_SINCOS && defined(__CUDA_ARCH__)
+    __sincosf(6.28318530718f * u, sn, cs);  // MUFU.SIN / MUFU.COS: abs. error ~5e-7 on [0, 2 pi], plenty for a sampling direction
+#else
+    sincospif(2.0f * u, sn, cs);
+#endif
+}
 // reciprocal as vec3::operator/ forms it (include/vec3.h:97): float(1.0 / double(t))
 template <bool X> __device__ __forceinline__ float recip(float t) {
     if (X) return (float)(1.0 / (double)t);
-    return __frcp_rn(t);
+    return fast_rcp(t);
 }
 template <bool X> __device__ __forceinline__ V3 div3(V3 v, float t) { return scale3<X>(recip<X>(t), v); }
-template <bool X> __device__ __forceinline__ float len3(V3 a) { return __fsqrt_rn(len2_3<X>(a)); }
+template <bool X> __device__ __forceinline__ float len3(V3 a) { return X ? __fsqrt_rn(len2_3<X>(a)) : fast_sqrt(len2_3<X>(a)); }
 template <bool X> __device__ __forceinline__ V3 unit3(V3 v) {
     if (X) return div3<true>(v, len3<true>(v));
     return scale3<false>(rsqrtf(len2_3<false>(v)), v);
@@ -162,10 +200,10 @@ template <int MODE, bool X> __device__ __forceinline__ V3 sample_ball(Rng<MODE>&
     } else {
         float u1 = rng.next(), u2 = rng.next(), u3 = rng.next();
         float z = 1.0f - 2.0f * u1;
-        float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+        float r = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));
         float sn, cs;
-        sincospif(2.0f * u2, &sn, &cs);
-        float rad = cbrtf(u3);
+        fast_sincos2pi(u2, &sn, &cs);
+        float rad = fast_cbrt01(u3);
         return mk3(rad * r * cs, rad * r * sn, rad * z);
     }
 }
@@ -176,9 +214,9 @@ template <int MODE, bool X> __device__ __forceinline__ V3 sample_unit(Rng<MODE>&
     } else {
         float u1 = rng.next(), u2 = rng.next();
         float z = 1.0f - 2.0f * u1;
-        float r = sqrtf(fmaxf(0.0f, 1.0f - z * z));
+        float r = fast_sqrt(fmaxf(0.0f, 1.0f - z * z));
         float sn, cs;
-        sincospif(2.0f * u2, &sn, &cs);
+        fast_sincos2pi(u2, &sn, &cs);
         return mk3(r * cs, r * sn, z);
     }
 }

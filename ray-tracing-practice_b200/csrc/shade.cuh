@@ -128,7 +128,8 @@ __device__ __forceinline__ bool shade_vertex(const DevScene& sc, int tex_mode, c
         float ratio = front ? recip<X>(ir) : ir;
         V3 ud = unit3<X>(d);
         float cos_t = fminf(dot3<X>(neg3(ud), n), 1.0f);
-        float sin_t = __fsqrt_rn(fsub<X>(1.0f, fmul<X>(cos_t, cos_t)));
+        float sin2 = fsub<X>(1.0f, fmul<X>(cos_t, cos_t));
+        float sin_t = X ? __fsqrt_rn(sin2) : fast_sqrt(sin2);
         bool tir = fmul<X>(ratio, sin_t) > 1.0f;
         V3 dir;
         if (tir || schlick<X>(cos_t, ratio) > rng.next()) dir = reflect3<X>(ud, n);

@@ -41,6 +41,9 @@ struct DevScene {
 // the first design; measured on B200 it is 10 % SLOWER than all-local (two LDS/STS + address math + a shared/local branch
 // per push and pop, and it takes L1 capacity away from the nodes), so the default is 0.  The builder guarantees
 // max_stack <= 64.
+#ifndef RTB_FAST_RCP
+#define RTB_FAST_RCP 1
+#endif
 #ifndef RTB_FAST_PLANE
 #define RTB_FAST_PLANE 1
 #endif
@@ -226,10 +229,19 @@ __device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, fl
     float dz = fabsf(d.z) < eps ? copysignf(eps, d.z) : d.z;
     r.o = o;
     r.d = d;
-    r.idx = 1.0f / dx; r.idy = 1.0f / dy; r.idz = 1.0f / dz;
+#if RTB_FAST_RCP && defined(__CUDA_ARCH__)
+    if (!X) {  // fast mode: MUFU.RCP (1 ulp) instead of the IEEE division sequence; these only steer the culling
+        r.idx = __fdividef(1.0f, dx); r.idy = __fdividef(1.0f, dy); r.idz = __fdividef(1.0f, dz);
+    } else
+#endif
+    { r.idx = 1.0f / dx; r.idy = 1.0f / dy; r.idz = 1.0f / dz; }
     r.oox = o.x * r.idx; r.ooy = o.y * r.idy; r.ooz = o.z * r.idz;
     r.a = len2_3<X>(d);
+#if RTB_FAST_RCP && defined(__CUDA_ARCH__)
+    r.inv_a = X ? 0.0f : __fdividef(1.0f, r.a);
+#else
     r.inv_a = X ? 0.0f : 1.0f / r.a;
+#endif
     r.tmin = tmin;
     r.closest = tmax;
     // conservative slab test: the far side is widened by a few ulps of the slab products (boxes are padded too)
