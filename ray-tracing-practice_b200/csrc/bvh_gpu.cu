@@ -138,38 +138,18 @@ __global__ void k_radix(const unsigned long long* __restrict__ keys, int n, int2
     parent[r] = i;
 }
 
-// ---- 5. bottom-up fit: the second thread to arrive at an inner node owns it
-__device__ __forceinline__ lbvh::CollapseDp load_dp(const lbvh::CollapseDp* dp, int node, int n) {
-    if (node >= n - 1) return lbvh::dp_leaf();
-    const float4 v = __ldcg(reinterpret_cast<const float4*>(dp + node));
-    lbvh::CollapseDp d;
-    d.c[0] = v.x; d.c[1] = v.y; d.c[2] = v.z;
-    d.k = __float_as_uint(v.w);
-    return d;
-}
-// the same thread fills the node's collapse table (lbvh.cuh, step 5b) from its children's
-__global__ void k_fit(const int2* __restrict__ children, const int* __restrict__ parent, int n, Box* boxes, lbvh::CollapseDp* dp,
-                      unsigned int* arrived) {
+// ---- 5. bottom-up fit: the second thread to arrive at an inner node owns it and everything below it (lbvh.cuh, fit_node:
+// tree rotation, box, collapse table)
+__global__ void k_fit(int2* children, int* parent, int n, Box* boxes, lbvh::CollapseDp* dp, unsigned int* arrived) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n || n < 2) return;
     int cur = parent[(n - 1) + p];
     while (true) {
         __threadfence();
         if (atomicAdd(&arrived[cur], 1u) == 0u) return;
-        int2 ch = children[cur];
-        // the children were written by other threads of this launch: read them from L2, not from this SM's L1
-        const float* a = reinterpret_cast<const float*>(boxes + ch.x);
-        const float* b = reinterpret_cast<const float*>(boxes + ch.y);
-        Box u;
-        for (int k = 0; k < 3; ++k) {
-            u.lo[k] = fminf(__ldcg(a + k), __ldcg(b + k));
-            u.hi[k] = fmaxf(__ldcg(a + 3 + k), __ldcg(b + 3 + k));
-        }
-        boxes[cur] = u;
-        const lbvh::CollapseDp d = lbvh::dp_inner(load_dp(dp, ch.x, n), load_dp(dp, ch.y, n), lbvh::box_area(u));
-        *reinterpret_cast<float4*>(dp + cur) = make_float4(d.c[0], d.c[1], d.c[2], __uint_as_float(d.k));
+        lbvh::fit_node(children, parent, boxes, dp, n, cur);
         if (cur == 0) return;
-        cur = parent[cur];
+        cur = __ldcg(parent + cur);
     }
 }
 

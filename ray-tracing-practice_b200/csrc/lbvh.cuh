@@ -283,6 +283,88 @@ LB_HD CollapseDp dp_inner(const CollapseDp& l, const CollapseDp& r, float area) 
     }
     return d;
 }
+// ---- step 5, the work at one inner node once both of its subtrees are final: an optional TREE ROTATION (swap one child with
+// a grandchild from the other side when that shrinks the box of the node in between; Kensler, "Tree rotations for improving
+// bounding volume hierarchies", RT 2008 -- the radix tree splits at Morton bit boundaries, not where the area says), then
+// the node's box and its collapse table.  Everything below `cur` belongs to the calling thread at this point (the other
+// arrival at `cur` has left), but was written by other threads of the same launch: on the device it is read with
+// ld.global.cg (L2), never from this SM's L1.  Measured on the 100k-sphere scene: 10.35 -> 10.08 wide-node visits per ray.
+#ifdef __CUDA_ARCH__
+#define LB_LDCG(p) __ldcg(p)
+#else
+#define LB_LDCG(p) (*(p))
+#endif
+#ifndef RTB_LBVH_ROTATE
+#define RTB_LBVH_ROTATE 1
+#endif
+LB_HD Box load_box_cg(const Box* b) {
+    const float* f = reinterpret_cast<const float*>(b);
+    Box r;
+    for (int k = 0; k < 3; ++k) { r.lo[k] = LB_LDCG(f + k); r.hi[k] = LB_LDCG(f + 3 + k); }
+    return r;
+}
+LB_HD CollapseDp load_dp_cg(const CollapseDp* dp, int node, int n) {
+    if (node >= n - 1) return dp_leaf();
+    const float4 v = LB_LDCG(reinterpret_cast<const float4*>(dp + node));
+    CollapseDp d;
+    d.c[0] = v.x; d.c[1] = v.y; d.c[2] = v.z;
+    union { float f; uint32_t u; } c;
+    c.f = v.w;
+    d.k = c.u;
+    return d;
+}
+LB_HD void store_dp(CollapseDp* dp, int node, const CollapseDp& d) {
+    union { float f; uint32_t u; } c;
+    c.u = d.k;
+    *reinterpret_cast<float4*>(dp + node) = make_float4(d.c[0], d.c[1], d.c[2], c.f);
+}
+LB_HD void fit_node(int2* children, int* parent, Box* boxes, CollapseDp* dp, int n, int cur) {
+    int2 ch = LB_LDCG(children + cur);
+    Box bl = load_box_cg(boxes + ch.x), br = load_box_cg(boxes + ch.y);
+#if RTB_LBVH_ROTATE
+    {
+        float best = 0.f;
+        int which = -1;
+        int2 cl = make_int2(-1, -1), cr = make_int2(-1, -1);
+        if (ch.y < n - 1) {  // right child is inner: candidates L <-> RL, L <-> RR
+            cr = LB_LDCG(children + ch.y);
+            const float ar = box_area(br);
+            const float g0 = LB_SUB(ar, box_area(box_union(bl, load_box_cg(boxes + cr.y))));
+            const float g1 = LB_SUB(ar, box_area(box_union(load_box_cg(boxes + cr.x), bl)));
+            if (g0 > best) { best = g0; which = 0; }
+            if (g1 > best) { best = g1; which = 1; }
+        }
+        if (ch.x < n - 1) {  // left child is inner: candidates R <-> LL, R <-> LR
+            cl = LB_LDCG(children + ch.x);
+            const float al = box_area(bl);
+            const float g2 = LB_SUB(al, box_area(box_union(br, load_box_cg(boxes + cl.y))));
+            const float g3 = LB_SUB(al, box_area(box_union(load_box_cg(boxes + cl.x), br)));
+            if (g2 > best) { best = g2; which = 2; }
+            if (g3 > best) { best = g3; which = 3; }
+        }
+        if (which >= 0) {
+            const int node = which < 2 ? ch.y : ch.x, other = which < 2 ? ch.x : ch.y;
+            int2 cn = which < 2 ? cr : cl;
+            const int moved = (which & 1) ? cn.y : cn.x;  // the grandchild that comes up to `cur`
+            if (which & 1) cn.y = other; else cn.x = other;
+            children[node] = cn;
+            parent[other] = node;
+            parent[moved] = cur;
+            if (which < 2) ch.x = moved; else ch.y = moved;
+            children[cur] = ch;
+            const Box nb = box_union(load_box_cg(boxes + cn.x), load_box_cg(boxes + cn.y));
+            boxes[node] = nb;
+            store_dp(dp, node, dp_inner(load_dp_cg(dp, cn.x, n), load_dp_cg(dp, cn.y, n), box_area(nb)));
+            // the two children of `cur` as they are now (the union below is the same box as before the rotation)
+            if (which < 2) { bl = load_box_cg(boxes + moved); br = nb; } else { bl = nb; br = load_box_cg(boxes + moved); }
+        }
+    }
+#endif
+    const Box u = box_union(bl, br);
+    boxes[cur] = u;
+    store_dp(dp, cur, dp_inner(load_dp_cg(dp, ch.x, n), load_dp_cg(dp, ch.y, n), box_area(u)));
+}
+
 // kids of the wide node rooted at binary inner node `bin` according to the tables; returns the number of INNER kids
 LB_HD int collapse_pick_dp(const int2* children, const CollapseDp* dp, int n, int bin, int kids[4]) {
     int nk = 0;

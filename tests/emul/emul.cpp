@@ -139,9 +139,7 @@ static void lbvh_build_host(const SphereIn* sp, int S, const PlaneIn* pl, int P,
         int cur = parent[(n - 1) + p];
         while (true) {
             if (arrived[cur]++ == 0) break;
-            const int l = children[cur].x, r = children[cur].y;
-            boxes[cur] = lbvh::box_union(boxes[l], boxes[r]);
-            dp[cur] = lbvh::dp_inner(l >= n - 1 ? lbvh::dp_leaf() : dp[l], r >= n - 1 ? lbvh::dp_leaf() : dp[r], lbvh::box_area(boxes[cur]));
+            lbvh::fit_node(children.data(), parent.data(), boxes.data(), dp.data(), n, cur);
             if (cur == 0) break;
             cur = parent[cur];
         }
