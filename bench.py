@@ -4,10 +4,10 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
 A step = one frame of the workload (default: BASELINE.json configs[2], the 100k-sphere 1080p / 256 spp / depth 32 scene
-the north_star target is quoted on) through the persistent megakernel.  A "ray" is one path segment (one hit_scene call
-of the reference).  N>1: launched by torchrun, one rank per GPU; every rank renders the tiles
-t % N == rank of the SAME frame (strong scaling) and the packed tiles are gathered to rank 0 over NCCL inside the step.
-Prints ONE JSON line on rank 0.
+the north_star target is quoted on) through the persistent megakernel, called through the C-ABI (rt_render_tiles).  A "ray"
+is one path segment (one hit_scene call of the reference).  N>1: launched by torchrun, one rank per
+GPU; every rank renders its interleaved tiles of the SAME frame (strong scaling) and the packed tiles are gathered to
+rank 0 with the library's own grouped ncclSend / ncclRecv inside the step.  Prints ONE JSON line on rank 0.
 """
 import argparse
 import json
@@ -84,12 +84,11 @@ class ClockSampler:
 
 
 def workload_scene(rt, name):
-    cfg = rt.CONFIGS[name]
-    hs = rt.synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
-    return cfg, hs
+    cfg, hs, tex = rt.workload(name)
+    return cfg, hs, tex
 
 
-def cpu_sample(hs, cfg, kind_pref="reference", target_s=12.0):
+def cpu_sample(hs, cfg, tex, kind_pref="reference", target_s=12.0):
     """reference CPU path on a bounded sample of the workload: every 8th pixel in x and y, spp scaled to ~target_s."""
     from oracle import oracle_py as O
     sp, pl, mt, _ = hs.arrays()
@@ -98,7 +97,7 @@ def cpu_sample(hs, cfg, kind_pref="reference", target_s=12.0):
         chk, kind = O.Ref(), "reference"
     else:
         chk, kind = O.Oracle(), "port"
-    sc = chk.scene(sp, pl, mt)
+    sc = chk.scene(sp, pl, mt, tex, 0 if tex is not None else -1)
     cam = hs.camera(0).copy()
     xs = ys = 8
     cam["samples_per_pixel"] = 1
@@ -121,9 +120,9 @@ def run_reference_arm(args, rank, world):
     if rank != 0:
         return
     import rtp_b200 as rt
-    cfg, hs = workload_scene(rt, args.workload)
+    cfg, hs, tex = workload_scene(rt, args.workload)
     # size one step to ~6 s so warmup+steps stay within minutes
-    base, sc, cam = cpu_sample(hs, cfg, "reference", target_s=6.0)
+    base, sc, cam = cpu_sample(hs, cfg, tex, "reference", target_s=6.0)
     threads = base["cores"]
     times, segs_total = [], 0
     for i in range(args.warmup + args.steps):
@@ -143,6 +142,20 @@ def run_reference_arm(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def latest_traffic_profile(workload):
+    """dram__bytes_read+write of one render_mega launch from the newest committed ncu --set full summary of this workload"""
+    import glob
+    best = None
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_mega_*.json"))):
+        try:
+            d = json.load(open(f))
+        except Exception:
+            continue
+        if d.get("workload", DEFAULT_WORKLOAD) == workload and "traffic_bytes_per_launch" in d:
+            best = (d["traffic_bytes_per_launch"], os.path.relpath(f, ROOT))
+    return best if best else (None, None)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -151,7 +164,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--kernel", default="mega", choices=["mega", "wavefront"])
-    ap.add_argument("--no-baselines", action="store_true", help="skip the cpu_baseline / reference-CUDA legs")
+    ap.add_argument("--no-baselines", action="store_true", help="skip the cpu_baseline / reference-CUDA / parity legs")
     ap.add_argument("--top-nodes", type=int, default=-1)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
@@ -168,25 +181,26 @@ def main():
     import torch
     import torch.distributed as dist
     import rtp_b200 as rt
-    from rtp_b200_pkg import multi_gpu as mg
 
     if rt.device_count() < 1:
         raise SystemExit("bench.py: no CUDA device -- this benchmark has no CPU path (" + rt.lib().rt_last_error().decode() + ")")
     torch.cuda.set_device(local_rank)
+    rt.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    comm = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+        comm = rt.Comm.from_torch(dist, dev)   # the library's own NCCL communicator (rt_comm_init_rank), id broadcast by torch
 
-    cfg, hs = workload_scene(rt, args.workload)
+    cfg, hs, tex = workload_scene(rt, args.workload)
     W, H, spp, depth = cfg["W"], cfg["H"], cfg["sqrt_spp"] ** 2, cfg["depth"]
-    scene = rt.Scene.from_host(hs)
+    sp, pl, mt, _ = hs.arrays()
+    scene = rt.Scene(sp, pl, mt, tex, 0 if tex is not None else -1)
     stats = scene.stats()
     cam = hs.camera(0)
     kernel = rt.KERNEL_MEGA if args.kernel == "mega" else rt.KERNEL_WAVEFRONT
     opts = dict(kernel=kernel, seed=0, top_nodes=args.top_nodes)
-    frame = mg.TiledFrame(scene, W, H, rank, world, dev)
-    stream = torch.cuda.current_stream().cuda_stream
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def barrier():
@@ -194,114 +208,135 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(timed):
-        flush.zero_()  # L2 flush between iterations (outside the event pair)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        frame.render(cam, stream, **opts)
-        full = frame.gather(dist, stream)
-        e1.record()
-        e1.synchronize()
-        info = scene.finish()
-        return e0.elapsed_time(e1), info, full
+    def step(host_fb=None):
+        """one frame through rt_render_tiles: this rank's tiles, NCCL gather to rank 0, unpack (and, with host_fb, the D2H of
+        the assembled frame on rank 0).  device_ms = CUDA events on the library's stream around render .. gather + unpack."""
+        flush.zero_()              # L2 flush between iterations, outside the timed events
+        torch.cuda.synchronize()
+        _, info = scene.render_tiles(comm, cam, out=host_fb, want_host=host_fb is not None, **opts)
+        return info
 
     for _ in range(max(args.warmup, 1)):
-        step(False)
+        step()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     t_wall = time.perf_counter()
-    ms_total, kms_total, segs = 0.0, 0.0, 0
+    dev_ms, kms, segs_total, rank_segs = 0.0, 0.0, 0, 0
     for _ in range(args.steps):
-        ms, info, full = step(True)
-        ms_total += ms
-        kms_total += info["kernel_ms"]
-        segs += info["segments"]
+        info = step()
+        dev_ms += info["device_ms"]
+        kms += info["kernel_ms"]
+        segs_total += info["segments_total"]       # rank 0: all ranks (the counts travel with the tiles)
+        rank_segs += info["segments_rank"]
     barrier()
     t_wall = time.perf_counter() - t_wall
     clocks = sampler.stop() if sampler else None
 
-    t = torch.tensor([ms_total, kms_total, float(segs)], dtype=torch.float64, device=dev)
+    t = torch.tensor([dev_ms, kms, float(rank_segs)], dtype=torch.float64, device=dev)
+    per_rank = None
     if world > 1:
-        tmax = t.clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone()
-        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms_total, kms_total, segs_all = tmax[0].item(), tmax[1].item(), tsum[2].item()
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        allt = torch.stack(allt).cpu().numpy()
+        ms_total, kms_max = float(allt[:, 0].max()), float(allt[:, 1].max())   # MAX over ranks
+        segs_all = float(allt[:, 2].sum())
+        k = allt[:, 1] / args.steps
+        per_rank = {"kernel_ms": {"min": float(k.min()), "mean": float(k.mean()), "max": float(k.max())},
+                    "kernel_ms_by_rank": [float(x) for x in k], "device_ms_by_rank": [float(x) for x in allt[:, 0] / args.steps],
+                    "segments_by_rank": [float(x) for x in allt[:, 2] / args.steps]}
     else:
-        segs_all = float(segs)
+        ms_total, kms_max, segs_all = dev_ms, kms, float(rank_segs)
     value = segs_all / (ms_total * 1e-3) / 1e6
     if args.kernel == "mega":
         chunked = spp >= 32  # rt_render_opts.sample_chunk auto: render_mega + reduce_chunks
-        launches_per_step = 1 + (1 if chunked else 0) + (1 if world > 1 else 0) + (1 if (world > 1 and rank == 0) else 0)  # render, reduce, pack, unpack(rank 0)
+        launches_per_step = 1 + (1 if chunked else 0) + (2 if world > 1 else 0)  # render, chunk sum; N>1: segment stash + pack (ranks > 0) / unpack (rank 0)
     else:
         K = max(1, min(spp, (16 << 20) // max(1, ((W + 15) // 16) * ((H + 15) // 16) * 256 // world)))
         launches_per_step = ((spp + K - 1) // K) * (2 + 2 * depth)
 
-    # ---- end to end through the public C-ABI call with HOST buffers (rt_render: launch + D2H of the sums), every rank
-    host_fb = np.zeros((H, W, 3), np.float32)
-    e2e_opts = dict(opts, tile_rank=rank, tile_nranks=world)
-    scene.render(cam, out=host_fb, **e2e_opts)
+    # ---- end to end through the public C-ABI call with HOST buffers: rt_render_tiles with a host framebuffer on rank 0 --
+    # launch, this rank's tiles, gather, unpack, ONE download of the assembled frame.  Wall clock, barriers on both sides.
+    host_fb = np.zeros((H, W, 3), np.float32) if rank == 0 else None
+    step(host_fb)
     barrier()
     t0 = time.perf_counter()
-    e2e_segs = 0
+    e2e_segs, e2e_d2h = 0, 0
     for _ in range(args.steps):
-        _, i2 = scene.render(cam, out=host_fb, **e2e_opts)
-        e2e_segs += i2["segments"]
+        i2 = scene.render_tiles(comm, cam, out=host_fb, want_host=rank == 0, **opts)[1]
+        e2e_segs += i2["segments_total"]
+        e2e_d2h = i2["d2h_bytes"]
     barrier()
     e2e_t = time.perf_counter() - t0
-    te = torch.tensor([e2e_t, float(e2e_segs)], dtype=torch.float64, device=dev)
     if world > 1:
-        tm = te.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
-        tsm = te.clone(); dist.all_reduce(tsm, op=dist.ReduceOp.SUM)
-        e2e_t, e2e_segs = tm[0].item(), tsm[1].item()
-    e2e_value = e2e_segs / e2e_t / 1e6
+        te = torch.tensor([e2e_t], dtype=torch.float64, device=dev)
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_t = te.item()
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+    e2e_value = e2e_segs / e2e_t / 1e6
 
     # ---- roofline of the dominant kernel (render_mega): FP32 issue, per SURVEY.md section 8d
     peaks, peak_src = load_peaks()
+    e2e_opts = dict(opts, tile_rank=rank, tile_nranks=world)
     _, cinfo = scene.render(cam, out=host_fb, count_work=True, **e2e_opts)
     fpr, bpr, per_ray = flops_per_ray(cinfo)
     sm_mhz = float(peaks.get("sm_max_mhz", 1965.0))
     fp32_peak = torch.cuda.get_device_properties(dev).multi_processor_count * FP32_LANES_PER_SM * 2 * sm_mhz * 1e6 / 1e12
-    kernel_rays_s = segs_all / world / (kms_total * 1e-3) if kms_total > 0 else 0.0  # per GPU, render kernel only
+    kernel_rays_s = segs_all / world / (kms_max * 1e-3) if kms_max > 0 else 0.0  # per GPU, render kernel only
     achieved = kernel_rays_s * fpr / 1e12
-    traffic, traffic_src = None, None
-    tp = os.path.join(ROOT, "profiles", "r01_ncu_mega_headline.json")   # dram__bytes_read+write of one render_mega launch (ncu --set full)
-    if args.workload == DEFAULT_WORKLOAD and args.kernel == "mega" and os.path.exists(tp):
-        traffic, traffic_src = json.load(open(tp))["traffic_bytes_per_launch"], "profiles/r01_ncu_mega_headline.json"
+    traffic, traffic_src = latest_traffic_profile(args.workload) if args.kernel == "mega" else (None, None)
+    compulsory = stats["device_bytes"] + W * H * 12
     roofline = {"bound": "fp32_issue", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": bpr * segs_all / world / args.steps, "kernel": "render_mega" if args.kernel == "mega" else "wf_extend",
-                "kernel_ms_per_launch": kms_total / args.steps, "flops_per_ray": fpr, "bytes_per_ray": bpr, "per_ray": per_ray,
+                "traffic": traffic, "traffic_source": traffic_src, "compulsory_dram_bytes_per_launch": compulsory,
+                "algorithmic_bytes_per_launch": bpr * segs_all / world / args.steps, "kernel": "render_mega" if args.kernel == "mega" else "wf_extend",
+                "kernel_ms_per_launch": kms_max / args.steps, "flops_per_ray": fpr, "bytes_per_ray": bpr, "per_ray": per_ray,
                 "peak_source": "148 SMs x 128 fp32 lanes x 2 x sm_max_mhz of MEASURED_PEAKS.json (%s); HBM %.0f GB/s (%s) is not the bound: "
                                "the working set is L2 resident" % (peak_src, peaks.get("hbm_gbs", 0), peak_src),
-                "hbm_algorithmic_gbs": kernel_rays_s * bpr / 1e9}
+                # SURVEY 8d's bytes/ray are what the traversal READS (nodes, primitives, materials) -- served by L1/L2, not by HBM
+                "l1_algorithmic_gbs": kernel_rays_s * bpr / 1e9,
+                "dram_gbs_measured": (traffic / (kms_max / args.steps * 1e-3) / 1e9) if traffic else None}
 
     line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "spheres": cfg["n"] + 94, "planes": 105, "width": W, "height": H, "spp": spp,
-                       "max_depth": depth, "kernel": args.kernel, "rng": "philox4x32-10", "parallelism": "tiles%d" % world,
+            "config": {"workload": args.workload, "spheres": stats["num_spheres"], "planes": stats["num_planes"], "width": W, "height": H,
+                       "spp": spp, "max_depth": depth, "kernel": args.kernel, "rng": "philox4x32-10", "parallelism": "tiles%d" % world,
+                       "floor_texture": "synthetic 2000x1330 RGBA float through the texture unit" if tex is not None else "none",
                        "l2": "flushed between timed steps (256 MB memset)", "bvh_nodes": stats["wide_nodes"],
-                       "bvh_depth": stats["wide_depth"], "bvh_build_ms": stats["build_ms"]},
+                       "bvh_depth": stats["wide_depth"], "bvh_build_ms": stats["build_ms"],
+                       "call": "rt_render_tiles (C-ABI): render own tiles -> grouped ncclSend/ncclRecv to rank 0 -> unpack"},
             "clocks": clocks, "kernel_only_mrays_s": kernel_rays_s / 1e6 * world,
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": int(W * H * 12 // world) * world,
-                    "call": "rt_render (camera struct in, host framebuffer out)"},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": int(e2e_d2h),
+                    "call": "rt_render_tiles (76-byte camera struct in; ONE assembled host framebuffer out on rank 0)"},
             "gpu_launches": launches_per_step * args.steps, "wall_s_timed_region": t_wall, "roofline": roofline}
+    if per_rank:
+        line["per_rank"] = per_rank
 
     if world == 1 and not args.no_baselines:
         try:
-            base, _, _ = cpu_sample(hs, cfg, "reference", target_s=12.0)
+            base, _, _ = cpu_sample(hs, cfg, tex, "reference", target_s=12.0)
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
         except Exception as e:  # the CPU leg must never take the GPU number down
             line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "unavailable", "sample": repr(e)}
         try:
-            line["reference_cuda"] = reference_cuda_leg(rt, scene, hs, cam, W, H, spp)
+            line["parity"] = parity_leg(rt, scene, hs, cam, sp, pl, mt, tex)
         except Exception as e:
-            line["reference_cuda"] = {"unavailable": repr(e)}
+            line["parity"] = {"unavailable": repr(e)}
+        try:
+            _, xi = scene.render(cam, out=host_fb, exact=True, **opts)   # same stream, same chunks, the reference's arithmetic
+            line["exact_mode_mrays_s"] = xi["segments"] / xi["kernel_ms"] / 1e3
+            line["exact_mode_kernel_ms"] = xi["kernel_ms"]
+        except Exception as e:
+            line["exact_mode_mrays_s"] = None
+            line["exact_mode_error"] = repr(e)
+        if W * H * spp <= 2 * 3840 * 2160 * 64:   # the 8K / 1024-spp frame would take the reference kernel minutes
+            try:
+                line["reference_cuda"] = reference_cuda_leg(rt, scene, hs, cam, sp, pl, mt, tex, kms_max / args.steps)
+            except Exception as e:
+                line["reference_cuda"] = {"unavailable": repr(e)}
         try:
             line["bvh_build"] = bvh_build_leg(rt, hs, cam, stats)
         except Exception as e:
@@ -309,6 +344,35 @@ def main():
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def parity_leg(rt, scene, hs, cam, sp, pl, mt, tex):
+    """north_star's id / t gate ON THE BENCHMARKED SCENE AND ARITHMETIC: every pixel-centre ray of the frame through
+    rt_trace_primary_ex(exact_math=0) -- the traversal + leaf code render_mega is compiled from -- against the checker: the
+    oracle's id-recording walk of the reference-built BVH (the oracle only checks here; nothing it computes is timed or
+    shipped), and against the library's own exact mode (which tests/ pin bit for bit to the reference's leaf tests)."""
+    rays = rt.pixel_center_rays(cam)
+    ty, ix, t = scene.trace_primary(rays, exact=False)
+    ey, ei, et = scene.trace_primary(rays, exact=True)
+    d = (ty != ey) | (ix != ei)
+    ok = ~d & (ey >= 0)
+    out = {"rays_checked": int(len(rays)), "arithmetic": "production (rt_trace_primary_ex exact_math=0)",
+           "id_mismatch_rate_vs_exact_mode": float(d.mean()), "id_mismatches_vs_exact_mode": int(d.sum()),
+           "max_rel_t_vs_exact_mode": float((np.abs(t[ok] - et[ok]) / et[ok]).max()) if ok.any() else 0.0}
+    try:
+        from oracle import oracle_py as O
+        osc = O.Oracle().scene(sp, pl, mt)
+        by, bi, brec = osc.trace(rays, 1)
+        m = (ty != by) | (ix != bi)
+        ok = ~m & (by >= 0)
+        out.update({"checker": "oracle: walk of the reference-built BVH with the reference leaf tests (include/bvh.h:19-65)",
+                    "id_mismatch_rate": float(m.mean()), "id_mismatches": int(m.sum()),
+                    "max_rel_t": float((np.abs(t[ok] - brec[ok, 0]) / brec[ok, 0]).max()) if ok.any() else 0.0,
+                    "exact_mode_id_mismatches": int(((ey != by) | (ei != bi)).sum())})
+        osc.close()
+    except Exception as e:
+        out["checker"] = "oracle unavailable: " + repr(e)
+    return out
 
 
 def bvh_build_leg(rt, hs, cam, host_stats):
@@ -331,20 +395,21 @@ def bvh_build_leg(rt, hs, cam, host_stats):
             "gpu_lbvh_render_kernel_ms": info["kernel_ms"]}
 
 
-def reference_cuda_leg(rt, scene, hs, cam, W, H, spp):
+def reference_cuda_leg(rt, scene, hs, cam, sp, pl, mt, tex, our_kernel_ms):
     """north_star baseline 1: the reference's own render_kernel (src/camera.cu:17), unmodified, built for sm_100 in
-    oracle/_ref, fed the same arrays.  Segments come from our kernel run on the reference's random stream (the reference
-    counts primary samples only)."""
+    oracle/_ref, fed the same arrays (and the same texture through its own texture object).  Segments come from our kernel
+    run on the reference's random stream (the reference counts primary samples only)."""
     from oracle import oracle_py as O
     if not O.ref_available():
         return {"unavailable": "oracle/_ref not built"}
     ref = O.Ref()
-    sp, pl, mt, _ = hs.arrays()
-    rs = ref.scene(sp, pl, mt)
+    rs = ref.scene(sp, pl, mt, tex, 0 if tex is not None else -1)
     _, info = scene.render(cam, rng=rt.RNG_REFERENCE)
     O.gpu_render_ref(rs, cam, reps=1)  # warm-up
     _, ms = O.gpu_render_ref(rs, cam, reps=2)
+    rs.close()
     return {"kernel_ms": ms, "mrays_s": info["segments"] / (ms * 1e-3) / 1e6, "segments": info["segments"],
+            "speedup_kernel_ms": ms / our_kernel_ms if our_kernel_ms > 0 else None,
             "note": "unmodified reference render_kernel, -O3 -arch=sm_100, same scene arrays + reference-built BVH"}
 
 

@@ -42,7 +42,8 @@ enum { RT_TEX_CPU = 0,         /* tex2D_cpu semantics: V flipped, no half texel 
        RT_TEX_GPU = 1 };       /* CUDA texture unit as the reference sets it up (src/main.cu:37-43) -- default */
 
 typedef struct rt_render_opts {
-    int struct_size;            /* = sizeof(rt_render_opts); 0-filled tail fields take defaults */
+    int struct_size;            /* = sizeof(rt_render_opts) as the caller compiled it: fields beyond it take their defaults
+                                   (<= 0: every field does) */
     int kernel;                 /* RT_KERNEL_* */
     int rng;                    /* RT_RNG_* */
     int exact_math;             /* 1: leaf tests + shading in the reference host build's exact operation order
@@ -53,9 +54,11 @@ typedef struct rt_render_opts {
                                    nranks <= 1 renders everything.  Pixels of other ranks are left untouched. */
     int count_work;             /* 1: also count node visits / leaf tests / shaded hits (slower; for the roofline) */
     int top_nodes_in_smem;      /* -1 default (megakernel: 0, others: 64); 0 off; N>0: stage the first N wide nodes in shared memory */
-    int sample_chunk;           /* megakernel work-item length in samples: 0 auto (2 for the Philox stream when spp >= 32, at most
-                                   128 chunks per pixel and ~3.3 GB of partial sums; chunk sums are added in chunk order, so the frame stays deterministic);
-                                   -1 never split a pixel (always the case for RT_RNG_REFERENCE: the reference's summation order) */
+    int sample_chunk;           /* megakernel work items split a pixel's samples into chunks that shrink geometrically (2/3 of what
+                                   is left each) down to THIS many samples, at most 6 chunks = 5 scratch planes of W*H*3 floats
+                                   (fewer when device memory is short); chunk sums are added in chunk order, so the frame stays
+                                   deterministic.  0 auto (2 for the Philox stream when spp >= 32); -1 never split a pixel (always
+                                   the case for RT_RNG_REFERENCE: the reference's summation order) */
 } rt_render_opts;
 
 typedef struct rt_work_counters {
@@ -122,9 +125,20 @@ int rt_render_finish(rt_scene* scene, unsigned long long* ray_segments, float* k
 /* Closest hit with primitive ids for caller-supplied rays (host arrays; rays6 = N x {ox,oy,oz,dx,dy,dz}).
  * prim_type: 0 sphere / 1 plane / -1 miss (BVHNode::type convention, include/bvh.h:11); prim_index: index into
  * the caller's original array; t: hit parameter in units of the UNNORMALISED direction, like HitRecord::t.
- * Always runs the exact-math leaf tests; parity target: the reference's leaf tests over all primitives. */
+ * Replaces hit_scene (include/scene.h:23-35) for rays the caller supplies.  rt_trace_primary runs the exact-math leaf
+ * tests (parity target: the reference's leaf tests over all primitives, bit for bit). */
 int rt_trace_primary(rt_scene* scene, const float* rays6, int num_rays, float tmin, float tmax, int* prim_type,
                      int* prim_index, float* t);
+typedef struct rt_trace_opts {
+    int struct_size;            /* = sizeof(rt_trace_opts) */
+    int exact_math;             /* 1: as rt_trace_primary.  0: the PRODUCTION arithmetic -- the traversal and leaf code the default
+                                   render (rt_render_opts.exact_math = 0) is compiled from: fast fp32 with FMA contraction, the
+                                   two-dot-product plane record, the un-widened slab test, SFU reciprocal / sqrt -- so ids and t
+                                   are the ones the benchmarked kernel shades */
+} rt_trace_opts;
+/* opts may be NULL (= rt_trace_primary). */
+int rt_trace_primary_ex(rt_scene* scene, const float* rays6, int num_rays, float tmin, float tmax, const rt_trace_opts* opts,
+                        int* prim_type, int* prim_index, float* t);
 
 /* Device-side output stage replacing ISaver::writeColor's arithmetic (src/camera.cu:136-148): byte =
  * (unsigned char)(256*clamp(sqrt(sum/divisor),0,0.999)).  d_fb_sum_rgb is a device pointer, rgb_u8 a host one. */
@@ -135,18 +149,58 @@ int rt_tonemap_u8(rt_scene* scene, const void* d_fb_sum_rgb, int width, int heig
 int rt_render_u8(rt_scene* scene, const void* camera_data76, const rt_render_opts* opts, int divisor, unsigned char* rgb_u8,
                  unsigned long long* ray_segments, float* kernel_ms);
 
-/* Tile partition helpers for the multi-GPU frame (tiles are RT_TILE x RT_TILE pixels, row-major tile ids). */
+/* Tile partition of the multi-GPU frame.  Tiles are RT_TILE x RT_TILE pixels with row-major ids; they are dealt to the
+ * ranks in groups of nranks consecutive ids, one tile of each group per rank, the position inside group g rotated by a
+ * hash of g (so that a rank does not own the same tile columns in every row).  rt_tile_owner gives the owning rank of a
+ * tile and k = its position in that rank's packed buffer (16x16x3 floats per tile, increasing k). */
 #define RT_TILE 16
+void rt_tile_owner(int tile, int nranks, int* rank, int* k);
 int rt_tiles_pack(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int rank, int nranks, void* d_packed,
                   void* cuda_stream);
 int rt_tiles_unpack(rt_scene* scene, const void* d_packed_all, int width, int height, int nranks, void* d_fb_sum_rgb,
                     void* cuda_stream);
 unsigned long long rt_tiles_packed_floats(int width, int height, int nranks); /* per-rank packed buffer length */
 
+/* ---- one frame on N GPUs (the reference is single-GPU: gpu_render -> Camera::render, src/camera.cu:290-349, :198-216).
+ * One rank per GPU -- a process (torchrun, MPI) or a thread of one process.  Every rank holds the whole scene (its own
+ * rt_scene on its own device) and calls rt_render_tiles with the same camera and options: each renders its interleaved
+ * tiles, the packed tiles go to rank 0 with grouped ncclSend / ncclRecv over NVLink, rank 0 assembles the frame on its
+ * device and downloads it once.  NCCL is bound at run time (dlopen); without it nranks > 1 fails with RT_ERR_UNSUPPORTED. */
+typedef struct rt_comm rt_comm;
+#define RT_COMM_ID_BYTES 128
+/* rank 0: an ncclUniqueId (RT_COMM_ID_BYTES bytes) to hand to every rank by the launcher's own means (MPI_Bcast, a
+ * torch.distributed broadcast, a file) */
+int rt_comm_unique_id(void* id_out);
+/* every rank, on its device (the calling thread's current device; see rt_set_device): ncclCommInitRank.  nranks == 1 needs no id. */
+int rt_comm_init_rank(const void* id, int rank, int nranks, rt_comm** out);
+/* one process driving ndev devices (devices NULL: 0..ndev-1): ncclCommInitAll; out receives ndev communicators, rank i on
+ * devices[i].  rt_render_tiles must then be called from ndev threads, one per rank. */
+int rt_comm_init_all(int ndev, const int* devices, rt_comm** out);
+void rt_comm_destroy(rt_comm* comm);
+int rt_comm_rank(const rt_comm* comm);
+int rt_comm_size(const rt_comm* comm);
+typedef struct rt_tiles_info {
+    int struct_size;                     /* = sizeof(rt_tiles_info), set by the caller */
+    int rank, nranks;
+    unsigned long long segments_rank;    /* path segments this rank traced */
+    unsigned long long segments_total;   /* rank 0: over all ranks (the counts travel with the tiles); 0 elsewhere */
+    float kernel_ms;                     /* this rank's render kernel (+ chunk sum) */
+    float device_ms;                     /* this rank's stream from the start of the render to the end of its send (rank 0:
+                                            of the gather and the unpack) -- CUDA events */
+    unsigned long long gathered_bytes;   /* rank 0: bytes received over NCCL */
+    unsigned long long d2h_bytes;        /* rank 0: bytes downloaded into fb_sum_rgb */
+} rt_tiles_info;
+/* comm NULL or of size 1: the whole frame on this device.  fb_sum_rgb: HOST buffer of W*H*3 floats on rank 0 (the
+ * reference's framebuffer contract, as rt_render); NULL there leaves the assembled frame in the scene's device framebuffer
+ * (rt_tonemap_u8(scene, NULL, ...) reads it); ignored on the other ranks.  opts->tile_rank / tile_nranks are taken from comm. */
+int rt_render_tiles(rt_scene* scene, rt_comm* comm, const void* camera_data76, const rt_render_opts* opts, float* fb_sum_rgb,
+                    rt_tiles_info* info);
+
 const char* rt_last_error(void);
 int rt_device_count(void);
-/* Selects the CUDA device of the CALLING THREAD for subsequent rt_scene_create calls (a scene lives on the device it was
- * created on).  The reference is single-GPU (it never calls cudaSetDevice); this is what the multi-GPU frame loop uses. */
+/* Selects the CUDA device of the CALLING THREAD for subsequent rt_scene_create / rt_comm_init_rank calls.  A scene lives
+ * on the device it was created on, and every entry point that takes a scene switches to that device for the duration of
+ * the call, so a handle may be used from any thread.  The reference is single-GPU (it never calls cudaSetDevice). */
 int rt_set_device(int device);
 const char* rt_version(void);
 

@@ -39,8 +39,11 @@ BVH_HOST_SAH, BVH_GPU_LBVH = 0, 1
 TILE = 16
 
 C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_rebuild", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
-                 "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_tonemap_u8", "rt_tiles_pack", "rt_tiles_unpack",
-                 "rt_tiles_packed_floats", "rt_last_error", "rt_device_count", "rt_set_device", "rt_version"]
+                 "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_trace_primary_ex", "rt_tonemap_u8", "rt_tiles_pack",
+                 "rt_tiles_unpack", "rt_tiles_packed_floats", "rt_tile_owner", "rt_comm_unique_id", "rt_comm_init_rank",
+                 "rt_comm_init_all", "rt_comm_destroy", "rt_comm_rank", "rt_comm_size", "rt_render_tiles", "rt_last_error",
+                 "rt_device_count", "rt_set_device", "rt_version"]
+COMM_ID_BYTES = 128
 
 
 class RtError(RuntimeError):
@@ -69,6 +72,16 @@ class SceneStats(C.Structure):
 
 class SceneOpts(C.Structure):
     _fields_ = [("struct_size", C.c_int), ("bvh_builder", C.c_int)]
+
+
+class TraceOpts(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("exact_math", C.c_int)]
+
+
+class TilesInfo(C.Structure):
+    _fields_ = [("struct_size", C.c_int), ("rank", C.c_int), ("nranks", C.c_int), ("segments_rank", C.c_ulonglong),
+                ("segments_total", C.c_ulonglong), ("kernel_ms", C.c_float), ("device_ms", C.c_float),
+                ("gathered_bytes", C.c_ulonglong), ("d2h_bytes", C.c_ulonglong)]
 
 
 def build(force=False):
@@ -100,6 +113,18 @@ def lib():
         L.rt_render_finish.argtypes = [vp, vp, vp, vp]
         L.rt_render_u8.argtypes = [vp, vp, vp, ci, vp, vp, vp]
         L.rt_trace_primary.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp]
+        L.rt_trace_primary_ex.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp, vp]
+        L.rt_tile_owner.restype = None
+        L.rt_tile_owner.argtypes = [ci, ci, vp, vp]
+        L.rt_comm_unique_id.argtypes = [vp]
+        L.rt_comm_init_rank.argtypes = [vp, ci, ci, vp]
+        L.rt_comm_init_all.argtypes = [ci, vp, vp]
+        L.rt_comm_destroy.restype = None
+        L.rt_comm_destroy.argtypes = [vp]
+        L.rt_comm_rank.argtypes = [vp]
+        L.rt_comm_size.argtypes = [vp]
+        L.rt_render_tiles.argtypes = [vp, vp, vp, vp, vp, vp]
+        L.rt_set_device.argtypes = [ci]
         L.rt_tonemap_u8.argtypes = [vp, vp, ci, ci, ci, vp]
         L.rt_tiles_pack.argtypes = [vp, vp, ci, ci, ci, ci, vp, vp]
         L.rt_tiles_unpack.argtypes = [vp, vp, ci, ci, ci, vp, vp]
@@ -124,6 +149,7 @@ def lib():
         L.rth_load_texels.argtypes = [C.c_char_p, vp, vp, vp]
         L.rth_bvh_check.argtypes = [vp, ci, vp, ci, vp, vp, vp]
         L.rth_gpu_render.argtypes = [vp, ci, C.c_char_p, ci]
+        L.rth_gpu_render_ex.argtypes = [vp, ci, ci, ci, C.c_char_p, ci]
         L.rth_set_output.argtypes = [vp, C.c_char_p, ci, ci, ci, ci, ci]
         _lib = L
     return _lib
@@ -193,10 +219,13 @@ class HostScene:
         lib().rth_camera_for_frame(self.h, frame, _ptr(cam))
         return cam
 
-    def gpu_render(self, fmt=0):
-        """gpu_render(SceneParams&, SceneData&) of the reference (src/camera.cu:290) over the C-ABI. Returns the log."""
+    def gpu_render(self, fmt=0, parity=False, pipeline=True, split_tiles=False, gpus=0):
+        """gpu_render(SceneParams&, SceneData&) of the reference (src/camera.cu:290) over the C-ABI. Returns the log.
+        parity: the reference's random stream + arithmetic (rt_main --parity); pipeline=False: files written inside the
+        frame loop like the reference; gpus / split_tiles: frames (or every frame's tiles) over several devices."""
         buf = C.create_string_buffer(1 << 16)
-        rc = lib().rth_gpu_render(self.h, fmt, buf, len(buf))
+        flags = (1 if parity else 0) | (0 if pipeline else 2) | (4 if split_tiles else 0)
+        rc = lib().rth_gpu_render_ex(self.h, fmt, flags, int(gpus), buf, len(buf))
         if rc != 0:
             raise RtError(rc, lib().rt_last_error().decode())
         return buf.value.decode()
@@ -344,12 +373,32 @@ class Scene:
         info.update(segments=segs.value, kernel_ms=ms.value)
         return info
 
-    def trace_primary(self, rays6, tmin=0.001, tmax=1e30):
+    def trace_primary(self, rays6, tmin=0.001, tmax=1e30, exact=True):
+        """closest hit ids / t.  exact=True: rt_trace_primary (reference leaf arithmetic); exact=False: rt_trace_primary_ex
+        with the production arithmetic of the default render."""
         rays = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
         n = len(rays)
         typ, idx, t = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float32)
-        _check(lib().rt_trace_primary(self.h, _ptr(rays), n, tmin, tmax, _ptr(typ), _ptr(idx), _ptr(t)))
+        if exact:
+            _check(lib().rt_trace_primary(self.h, _ptr(rays), n, tmin, tmax, _ptr(typ), _ptr(idx), _ptr(t)))
+        else:
+            to = TraceOpts(C.sizeof(TraceOpts), 0)
+            _check(lib().rt_trace_primary_ex(self.h, _ptr(rays), n, tmin, tmax, C.byref(to), _ptr(typ), _ptr(idx), _ptr(t)))
         return typ, idx, t
+
+    def render_tiles(self, comm, cam, out=None, want_host=True, **kw):
+        """rt_render_tiles: this rank's share of one frame + the NCCL gather to rank 0.  Returns (frame or None, info)."""
+        cam = np.ascontiguousarray(cam, CAMERA)
+        W, H = int(cam["image_width"][0]), int(cam["image_height"][0])
+        rank0 = comm is None or comm.rank == 0
+        fb = None
+        if rank0 and want_host:
+            fb = out if out is not None else np.zeros((H, W, 3), np.float32)
+        o = self._opts(**kw)
+        ti = TilesInfo()
+        ti.struct_size = C.sizeof(TilesInfo)
+        _check(lib().rt_render_tiles(self.h, comm.h if comm is not None else None, _ptr(cam), C.byref(o), _ptr(fb), C.byref(ti)))
+        return fb, {n: getattr(ti, n) for n, _ in TilesInfo._fields_ if n != "struct_size"}
 
     def tonemap_u8(self, W, H, divisor, d_fb_ptr=None):
         out = np.zeros((H, W, 3), np.uint8)
@@ -372,6 +421,59 @@ class Scene:
 
 def tiles_packed_floats(W, H, nranks):
     return int(lib().rt_tiles_packed_floats(W, H, nranks))
+
+
+def tile_owner(tile, nranks):
+    """(rank, k) of a tile id under the interleaved partition (rt_tile_owner; host arithmetic, no GPU needed)"""
+    r, k = C.c_int(), C.c_int()
+    lib().rt_tile_owner(int(tile), int(nranks), C.byref(r), C.byref(k))
+    return r.value, k.value
+
+
+def set_device(dev):
+    _check(lib().rt_set_device(int(dev)))
+
+
+class Comm:
+    """rt_comm: the NCCL communicator of a tile-partitioned frame, one rank per GPU."""
+
+    def __init__(self, handle, rank, nranks):
+        self.h, self.rank, self.nranks = handle, rank, nranks
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_char * COMM_ID_BYTES)()
+        _check(lib().rt_comm_unique_id(buf))
+        return bytes(buf)
+
+    @classmethod
+    def init_rank(cls, uid, rank, nranks):
+        h = C.c_void_p()
+        _check(lib().rt_comm_init_rank(uid, rank, nranks, C.byref(h)))
+        return cls(h, rank, nranks)
+
+    @classmethod
+    def init_all(cls, ndev, devices=None):
+        hs = (C.c_void_p * ndev)()
+        dv = (C.c_int * ndev)(*devices) if devices is not None else None
+        _check(lib().rt_comm_init_all(ndev, dv, hs))
+        return [cls(C.c_void_p(hs[i]), i, ndev) for i in range(ndev)]
+
+    @classmethod
+    def from_torch(cls, dist, device):
+        """one rank per process under torch.distributed: rank 0's id is broadcast as a byte tensor"""
+        import torch
+        rank, world = dist.get_rank(), dist.get_world_size()
+        t = torch.zeros(COMM_ID_BYTES, dtype=torch.uint8, device=device)
+        if rank == 0:
+            t.copy_(torch.frombuffer(bytearray(cls.unique_id()), dtype=torch.uint8))
+        dist.broadcast(t, 0)
+        return cls.init_rank(bytes(t.cpu().numpy().tobytes()), rank, world)
+
+    def close(self):
+        if self.h:
+            lib().rt_comm_destroy(self.h)
+            self.h = C.c_void_p()
 
 
 def pixel_center_rays(cam):
@@ -445,7 +547,20 @@ CONFIGS = {
     "spheres100k_1080p_256spp_d32": dict(n=100000, W=1920, H=1080, sqrt_spp=16, depth=32),
     "spheres1m_4k_64spp_d8": dict(n=1000000, W=3840, H=2160, sqrt_spp=8, depth=8),
     "spheres100k_8k_1024spp_d32": dict(n=100000, W=7680, H=4320, sqrt_spp=32, depth=32),
+    # BASELINE.json configs[0]: the reference's shipped config.txt scene (94 spheres + 105 planes, camera path, depth 50,
+    # 2500 spp) WITH a floor texture of floor.jpg's shape through the texture unit (floor.jpg itself cannot travel)
+    "shipped_textured_1080x720_2500spp_d50": dict(kind="shipped", n=0, W=1080, H=720, sqrt_spp=50, depth=50),
 }
+
+
+def workload(name):
+    """(cfg, HostScene, texture or None) of a named BASELINE workload"""
+    cfg = CONFIGS[name]
+    if cfg.get("kind") == "shipped":
+        hs = HostScene(shipped_config_text(W=cfg["W"], H=cfg["H"], max_depth=cfg["depth"], sqrt_spp=cfg["sqrt_spp"]), texture="")
+        return cfg, hs, synthetic_texture()
+    hs = synthetic_scene(cfg["n"], W=cfg["W"], H=cfg["H"], sqrt_spp=cfg["sqrt_spp"], depth=cfg["depth"], seed=1234, texture="")
+    return cfg, hs, None
 
 
 def synthetic_scene(n_spheres, W=1920, H=1080, sqrt_spp=8, depth=16, seed=1234, texture=""):

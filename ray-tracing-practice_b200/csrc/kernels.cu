@@ -82,8 +82,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
                     acc = add3<X>(acc, ps.L);
                     ++sample;
-                    if (sample >= min(spp, (chunk + 1) * fp.chunk_spp)) {
-                        float* out = (nchunks > 1 ? fp.part + (size_t)chunk * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
+                    if (sample >= fp.chunk_start[chunk + 1]) {
+                        float* out = (chunk > 0 ? fp.part + (size_t)(chunk - 1) * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
                         out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
                         has_pixel = false;
                     }
@@ -99,13 +99,16 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     unsigned k = 0;
                     if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
                     k = __shfl_sync(full, k, 0);
-                    const unsigned kb = k / (unsigned)nchunks;  // item = (tile, 8x4 block, sample chunk), chunk fastest
-                    if ((int)(kb / kBlocksPerTile) >= fp.my_tiles) { exhausted = true; break; }
-                    const int tile = (int)(kb / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
+                    // item = (sample chunk, tile, 8x4 block), chunk slowest: the long chunks of every block come first,
+                    // the short ones make up the end of the frame
+                    const unsigned per_chunk = (unsigned)fp.my_tiles * kBlocksPerTile;
+                    if (k >= per_chunk * (unsigned)nchunks) { exhausted = true; break; }
+                    const unsigned kb = k % per_chunk;
+                    const int tile = tile_of_rank((int)(kb / kBlocksPerTile), fp.tile_rank, fp.tile_nranks);  // >= tile count: no pixels
                     const int blk = (int)(kb % kBlocksPerTile);  // 8 blocks of 8x4 pixels inside the 16x16 tile
                     pool_x0 = (tile % fp.tiles_x) * kTile + (blk & 1) * 8;
                     pool_y0 = (tile / fp.tiles_x) * kTile + (blk >> 1) * 4;
-                    pool_chunk = (int)(k % (unsigned)nchunks);
+                    pool_chunk = (int)(k / per_chunk);
                     pool_next = 0;
                 }
                 int avail = kBlockPixels - pool_next;
@@ -121,7 +124,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                         has_pixel = true;
                         px = x; py = y;
                         chunk = pool_chunk;
-                        sample = pool_chunk * fp.chunk_spp;
+                        sample = fp.chunk_start[pool_chunk];
                         acc = mk3(0, 0, 0);
                         pixel_base = pixel_seed_base(x, y, W);
                     }
@@ -226,6 +229,12 @@ cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rn
 }
 
 // ---------------------------------------------------------------- primary-ray closest hit (parity entry point)
+// X = true: the exact-math leaf tests (the reference's operation order, include/sphere.h:24-47, include/plane.h:57-96).
+// X = false: the PRODUCTION arithmetic -- the very functions render_mega<.., false, ..> is built from (trav_begin with the
+// hoisted primitives, trav_leaf_pop -> sphere_t<false> / plane_fast_t, trav_inner<false> with the un-widened slab test, the
+// SFU approximations as compiled for the device), driven by the megakernel's own loop shape, so the ids / t this entry
+// point returns are the ids / t the benchmarked kernel shades.
+template <bool X>
 __global__ void __launch_bounds__(256, 2) trace_primary_kernel(const __grid_constant__ DevScene sc, const float* __restrict__ rays6,
                                                                int n, float tmin, float tmax, int* __restrict__ type,
                                                                int* __restrict__ index, float* __restrict__ t) {
@@ -238,46 +247,96 @@ __global__ void __launch_bounds__(256, 2) trace_primary_kernel(const __grid_cons
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float* r = rays6 + 6 * (size_t)i;
         HitInfo hit;
-        trace_closest<true, false>(sc, s_top, s_st, s_sr, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), tmin, tmax, hit, wc);
+        if (X) {
+            trace_closest<true, false>(sc, s_top, s_st, s_sr, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), tmin, tmax, hit, wc);
+        } else {
+            float2 lstack[kLocalStack];
+            TravStack stk;
+            stk.st = s_st; stk.sr = s_sr; stk.lo = lstack;
+            stk.tid = threadIdx.x; stk.nt = blockDim.x;
+            RayTrav rt;
+            trav_begin<false, false>(sc, rt, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), tmin, tmax, wc);
+            while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {  // render_mega's TRACE loop (RTB_LOOP_SHAPE 1)
+                if (ref_is_leaf(rt.ref)) trav_leaf_pop<false, false>(sc, rt, stk, wc);
+                if (ref_is_inner(rt.ref)) {
+                    if (trav_inner<false, false, true>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+                }
+            }
+            hit = trav_hit(rt);
+            if (rt.htype >= 0)  // fast mode does not carry the caller's index through the traversal
+                hit.orig = rt.htype == 0 ? __ldg(sc.sphere_meta + rt.hslot).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)rt.hslot + 3).w);
+        }
         type[i] = hit.type;
         index[i] = hit.orig;
         t[i] = hit.type < 0 ? 0.0f : hit.t;
     }
 }
 
-cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
-                                 int* d_index, float* d_t, cudaStream_t stream) {
+template <bool X>
+static cudaError_t launch_trace_primary_t(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
+                                          int* d_index, float* d_t, int num_sms, cudaStream_t stream) {
     const int threads = 256;
     size_t smem = mega_smem_bytes(sc.top_nodes, threads);
-    cudaError_t e = cudaFuncSetAttribute(trace_primary_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(trace_primary_kernel<X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int blocks = (n + threads - 1) / threads;
-    if (blocks > 148 * 2 * 4) blocks = 148 * 2 * 4;
+    if (blocks > num_sms * 2 * 4) blocks = num_sms * 2 * 4;
     if (blocks < 1) blocks = 1;
-    trace_primary_kernel<<<blocks, threads, smem, stream>>>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t);
+    trace_primary_kernel<X><<<blocks, threads, smem, stream>>>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t);
     return cudaGetLastError();
+}
+cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int exact, int* d_type,
+                                 int* d_index, float* d_t, int num_sms, cudaStream_t stream) {
+    return exact ? launch_trace_primary_t<true>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t, num_sms, stream)
+                 : launch_trace_primary_t<false>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t, num_sms, stream);
 }
 
 // ---------------------------------------------------------------- sum of the sample chunks (render_mega with nchunks > 1)
+// fb holds chunk 0's sums, part[c-1] chunk c's: fb = ((fb + part[0]) + part[1]) + ... for the pixels of this rank's tiles
+// (the other pixels of the planes were never written).  A tile row is 48 consecutive floats; when rows are 16-byte aligned
+// (W % 4 == 0) a thread handles one float4 of them, 12 per row, 192 per tile.
+template <bool VEC>
 __global__ void reduce_chunks_kernel(const __grid_constant__ FrameParams fp) {
     const int W = fp.cam.W, H = fp.cam.H;
     const size_t plane = (size_t)W * H * 3;
+    const int ntiles = fp.tiles_x * fp.tiles_y;
     for (int k = blockIdx.x; k < fp.my_tiles; k += gridDim.x) {
-        int t = k * fp.tile_nranks + fp.tile_rank;
-        int x = (t % fp.tiles_x) * kTile + (threadIdx.x & 15), y = (t / fp.tiles_x) * kTile + (threadIdx.x >> 4);
-        if (x < W && y < H) {
-            size_t i = 3 * ((size_t)y * W + x);
-            float r = fp.part[i], g = fp.part[i + 1], b = fp.part[i + 2];
-            for (int c = 1; c < fp.nchunks; ++c) {
-                const float* p = fp.part + c * plane + i;
-                r += p[0]; g += p[1]; b += p[2];
+        const int t = tile_of_rank(k, fp.tile_rank, fp.tile_nranks);
+        if (t >= ntiles) continue;
+        const int x0 = (t % fp.tiles_x) * kTile, y0 = (t / fp.tiles_x) * kTile;
+        if (VEC) {
+            const int row = threadIdx.x / 12, q = threadIdx.x % 12;  // 16 rows x 12 float4
+            const int y = y0 + row, x = x0 + (q * 4) / 3;            // first pixel the float4 touches
+            if (row < kTile && y < H && x < W) {                     // W % 4 == 0 and x0 % 16 == 0: a float4 never straddles the row end
+                const size_t i = 3 * ((size_t)y * W + x0) + 4 * (size_t)q;
+                float4 a = *reinterpret_cast<const float4*>(fp.fb + i);
+                for (int c = 0; c + 1 < fp.nchunks; ++c) {
+                    const float4 b = __ldcs(reinterpret_cast<const float4*>(fp.part + c * plane + i));
+                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+                }
+                *reinterpret_cast<float4*>(fp.fb + i) = a;
             }
-            fp.fb[i] = r; fp.fb[i + 1] = g; fp.fb[i + 2] = b;
+        } else {
+            for (int p = threadIdx.x; p < kTile * kTile; p += blockDim.x) {
+                const int x = x0 + (p & 15), y = y0 + (p >> 4);
+                if (x < W && y < H) {
+                    const size_t i = 3 * ((size_t)y * W + x);
+                    float r = fp.fb[i], g = fp.fb[i + 1], b = fp.fb[i + 2];
+                    for (int c = 0; c + 1 < fp.nchunks; ++c) {
+                        const float* q = fp.part + c * plane + i;
+                        r += q[0]; g += q[1]; b += q[2];
+                    }
+                    fp.fb[i] = r; fp.fb[i + 1] = g; fp.fb[i + 2] = b;
+                }
+            }
         }
     }
 }
-cudaError_t launch_reduce_chunks(const FrameParams& fp, cudaStream_t stream) {
-    reduce_chunks_kernel<<<148 * 8, kTile * kTile, 0, stream>>>(fp);
+cudaError_t launch_reduce_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream) {
+    // vector path: rows of the frame AND of every plane 16-byte aligned (cudaMalloc bases are; W % 4 == 0 keeps the rows)
+    const bool vec = fp.cam.W % 4 == 0 && ((uintptr_t)fp.fb & 15) == 0 && ((uintptr_t)fp.part & 15) == 0;
+    if (vec) reduce_chunks_kernel<true><<<num_sms * 8, 192, 0, stream>>>(fp);
+    else reduce_chunks_kernel<false><<<num_sms * 8, 256, 0, stream>>>(fp);
     return cudaGetLastError();
 }
 
@@ -290,30 +349,30 @@ __global__ void tonemap_kernel(const float* __restrict__ fb, size_t n, float inv
         out[i] = (unsigned char)(int)__fmul_rn(256.0f, v);
     }
 }
-cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, cudaStream_t stream) {
+cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, int num_sms, cudaStream_t stream) {
     float inv = (float)(1.0 / (double)(float)divisor);
     int blocks = (int)((n_values + 255) / 256);
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > num_sms * 8) blocks = num_sms * 8;
     if (blocks < 1) blocks = 1;
     tonemap_kernel<<<blocks, 256, 0, stream>>>(d_fb, n_values, inv, d_out);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- tile pack / unpack for the multi-GPU gather
-// rank r owns tiles t with t % nranks == r; its packed buffer holds them in increasing t, 16x16x3 floats each.
+// rank r's packed buffer holds its tiles in increasing k (kernels.h: tile_of_rank), 16x16x3 floats each.
 size_t tiles_packed_floats(int W, int H, int nranks) {
     size_t tiles = (size_t)((W + kTile - 1) / kTile) * ((H + kTile - 1) / kTile);
     size_t per = (tiles + nranks - 1) / nranks;
     return per * kTile * kTile * 3;
 }
 __global__ void tiles_pack_kernel(const float* __restrict__ fb, int W, int H, int rank, int nranks, float* __restrict__ packed) {
-    int tiles_x = (W + kTile - 1) / kTile, tiles_y = (H + kTile - 1) / kTile;
-    int my = (tiles_x * tiles_y - rank + nranks - 1) / nranks;
+    const int tiles_x = (W + kTile - 1) / kTile, ntiles = tiles_x * ((H + kTile - 1) / kTile);
+    const int my = (ntiles + nranks - 1) / nranks;
     for (int k = blockIdx.x; k < my; k += gridDim.x) {
-        int t = k * nranks + rank;
-        int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
+        const int t = tile_of_rank(k, rank, nranks);
+        const int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
         float* dst = packed + ((size_t)k * kTile * kTile + threadIdx.x) * 3;
-        if (x < W && y < H) {
+        if (t < ntiles && x < W && y < H) {
             const float* src = fb + 3 * ((size_t)y * W + x);
             dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
         } else {
@@ -321,11 +380,14 @@ __global__ void tiles_pack_kernel(const float* __restrict__ fb, int W, int H, in
         }
     }
 }
-__global__ void tiles_unpack_kernel(const float* __restrict__ all, int W, int H, int nranks, size_t per_rank, float* __restrict__ fb) {
-    int tiles_x = (W + kTile - 1) / kTile, tiles_y = (H + kTile - 1) / kTile;
-    for (int t = blockIdx.x; t < tiles_x * tiles_y; t += gridDim.x) {
-        int r = t % nranks, k = t / nranks;
-        int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
+__global__ void tiles_unpack_kernel(const float* __restrict__ all, int W, int H, int nranks, int skip_rank, size_t per_rank,
+                                    float* __restrict__ fb) {
+    const int tiles_x = (W + kTile - 1) / kTile, ntiles = tiles_x * ((H + kTile - 1) / kTile);
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        int r, k;
+        tile_owner(t, nranks, r, k);
+        if (r == skip_rank) continue;
+        const int x = (t % tiles_x) * kTile + (threadIdx.x & 15), y = (t / tiles_x) * kTile + (threadIdx.x >> 4);
         if (x < W && y < H) {
             const float* src = all + (size_t)r * per_rank + ((size_t)k * kTile * kTile + threadIdx.x) * 3;
             float* dst = fb + 3 * ((size_t)y * W + x);
@@ -333,12 +395,13 @@ __global__ void tiles_unpack_kernel(const float* __restrict__ all, int W, int H,
         }
     }
 }
-cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, cudaStream_t stream) {
-    tiles_pack_kernel<<<148 * 4, kTile * kTile, 0, stream>>>(d_fb, W, H, rank, nranks, d_packed);
+cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, int num_sms, cudaStream_t stream) {
+    tiles_pack_kernel<<<num_sms * 4, kTile * kTile, 0, stream>>>(d_fb, W, H, rank, nranks, d_packed);
     return cudaGetLastError();
 }
-cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, float* d_fb, cudaStream_t stream) {
-    tiles_unpack_kernel<<<148 * 4, kTile * kTile, 0, stream>>>(d_packed_all, W, H, nranks, tiles_packed_floats(W, H, nranks), d_fb);
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, float* d_fb, int num_sms,
+                                cudaStream_t stream) {
+    tiles_unpack_kernel<<<num_sms * 4, kTile * kTile, 0, stream>>>(d_packed_all, W, H, nranks, skip_rank, tiles_packed_floats(W, H, nranks), d_fb);
     return cudaGetLastError();
 }
 

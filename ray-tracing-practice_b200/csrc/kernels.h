@@ -7,6 +7,8 @@
 
 namespace rtb {
 
+constexpr int kMaxChunks = 8;
+
 struct FrameParams {
     CameraPod cam;
     uint2 key;          // Philox key
@@ -16,10 +18,13 @@ struct FrameParams {
     int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
     int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
     float* fb;                        // W*H*3 sums
-    // sample chunks (render_mega only): a work item is (8x4 pixel block, chunk of chunk_spp samples); with nchunks > 1 a
-    // lane writes its chunk's partial sum to part[chunk][pixel] and reduce_chunks adds the chunks in order into fb
+    // sample chunks (render_mega only): a work item is (8x4 pixel block, samples [chunk_start[c], chunk_start[c+1])).  Chunk 0
+    // accumulates into fb itself, chunk c > 0 into part[c-1][pixel], and reduce_chunks adds the planes to fb in chunk order.
+    // Chunks shrink geometrically (the long ones are queued first, the short ones form the end of the frame), so a handful of
+    // planes gives the frame a tail of a few samples per lane.
     float* part;
-    int chunk_spp, nchunks;
+    int nchunks;
+    int chunk_start[kMaxChunks + 1];
     unsigned int* tile_counter;       // work queue head (zeroed before launch)
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
 };
@@ -31,6 +36,25 @@ struct LaunchCfg {
 };
 
 constexpr int kTile = 16;  // == RT_TILE
+
+// Interleaved-tile partition of a frame over `nranks` devices.  Tiles (row-major ids) are dealt in groups of nranks
+// consecutive ids, one tile of every group to every rank; WHICH tile of group g a rank gets is rotated by a hash of g.
+// (Plain t % nranks hands a rank the same tile COLUMNS in every row whenever the tiles per row are a multiple of nranks --
+// 120 tiles at 1080p, 480 at 8K, for 2 / 4 / 8 ranks -- i.e. vertical stripes, and a rank's cost then follows whatever
+// the picture holds in its stripes.)  k = the rank's k-th tile = group index; rank r's packed buffer holds its tiles in
+// increasing k.  The last group may be short: a (k, rank) whose tile id is >= the tile count owns nothing.
+__host__ __device__ inline int tile_rot(unsigned int g, int nranks) {
+    return nranks > 1 ? (int)(((g * 0x9E3779B1u) >> 16) % (unsigned int)nranks) : 0;
+}
+__host__ __device__ inline int tile_of_rank(int k, int rank, int nranks) {
+    int p = rank - tile_rot((unsigned int)k, nranks);
+    if (p < 0) p += nranks;
+    return k * nranks + p;
+}
+__host__ __device__ inline void tile_owner(int t, int nranks, int& rank, int& k) {
+    k = t / nranks;
+    rank = (t % nranks + tile_rot((unsigned int)k, nranks)) % nranks;
+}
 // the unit of work a warp fetches with one atomicAdd: an 8x4-pixel block (one pixel per lane) of a 16x16 tile.  Tiles
 // stay the unit of the multi-GPU partition; blocks keep the end-of-frame tail short (8x more, 8x smaller work items).
 constexpr int kBlockPixels = 32;
@@ -59,13 +83,16 @@ struct WavefrontScratch {
 };
 cudaError_t launch_render_wavefront(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
                                     WavefrontScratch& scratch, cudaStream_t stream);
-cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int* d_type,
-                                 int* d_index, float* d_t, cudaStream_t stream);
-// fb[pixel] = part[0][pixel] + part[1][pixel] + ... (in chunk order: deterministic) for the pixels of this rank's tiles
-cudaError_t launch_reduce_chunks(const FrameParams& fp, cudaStream_t stream);
-cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, cudaStream_t stream);
-cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, cudaStream_t stream);
-cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, float* d_fb, cudaStream_t stream);
+// exact = 1: the reference's leaf arithmetic; 0: the production (fast fp32 + SFU) arithmetic of render_mega
+cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int exact, int* d_type,
+                                 int* d_index, float* d_t, int num_sms, cudaStream_t stream);
+// fb[pixel] += part[0][pixel] + part[1][pixel] + ... (in chunk order: deterministic) for the pixels of this rank's tiles
+cudaError_t launch_reduce_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream);
+cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, int num_sms, cudaStream_t stream);
+cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, int num_sms, cudaStream_t stream);
+// skip_rank >= 0: leave that rank's tiles alone (they are already in d_fb: the caller rendered them there)
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, float* d_fb, int num_sms,
+                                cudaStream_t stream);
 size_t tiles_packed_floats(int W, int H, int nranks);
 size_t mega_smem_bytes(int top_nodes, int threads);
 

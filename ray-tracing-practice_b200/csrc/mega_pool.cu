@@ -28,7 +28,7 @@ __device__ __forceinline__ bool take_pixel(const FrameParams& fp, WarpSched& ws,
             if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
             k = __shfl_sync(full, k, 0);
             if ((int)(k / kBlocksPerTile) >= fp.my_tiles) { ws.exhausted = true; break; }
-            ws.pool_tile = (int)(k / kBlocksPerTile) * fp.tile_nranks + fp.tile_rank;
+            ws.pool_tile = tile_of_rank((int)(k / kBlocksPerTile), fp.tile_rank, fp.tile_nranks);
             ws.pool_blk = (int)(k % kBlocksPerTile);
             ws.pool_next = 0;
         }

@@ -12,68 +12,19 @@
 #include <string>
 #include <vector>
 
-#include "../../include/rt_b200.h"
 #include "bvh_gpu.h"
-#include "kernels.h"
+#include "rt_scene_impl.h"
 #include "scene_pack.h"
 #include "wide_bvh.h"
 
 using namespace rtb;
 
-namespace {
-
-thread_local std::string g_err;
-
-int fail(int code, const std::string& msg) {
-    g_err = msg;
-    return code;
+namespace rtb {
+std::string& last_error() {
+    thread_local std::string e;
+    return e;
 }
-#define RT_CUDA(expr)                                                                                              \
-    do {                                                                                                           \
-        cudaError_t e_ = (expr);                                                                                   \
-        if (e_ != cudaSuccess) {                                                                                   \
-            char b_[512];                                                                                          \
-            snprintf(b_, sizeof b_, "CUDA error = %u (%s) at %s:%d '%s'", (unsigned)e_, cudaGetErrorString(e_), __FILE__, \
-                     __LINE__, #expr);                                                                             \
-            cudaGetLastError();                                                                                    \
-            return fail(RT_ERR_CUDA, b_);                                                                          \
-        }                                                                                                          \
-    } while (0)
-
-}  // namespace
-
-struct rt_scene {
-    int device = 0;
-    int num_sms = 148;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    rt_scene_stats stats{};
-    DevScene dev{};
-    int default_top = 0;
-    // owned device memory
-    void* d_nodes = nullptr;
-    void* d_spheres = nullptr;
-    void* d_sphere_meta = nullptr;
-    void* d_planes = nullptr;
-    void* d_planes_fast = nullptr;
-    void* d_mats = nullptr;
-    void* d_tex = nullptr;
-    cudaArray_t tex_array = nullptr;
-    cudaTextureObject_t tex_obj = 0;
-    float* d_fb = nullptr;
-    size_t fb_floats = 0;
-    unsigned char* d_u8 = nullptr;
-    size_t u8_bytes = 0;
-    unsigned int* d_tile_counter = nullptr;
-    unsigned long long* d_counters = nullptr;
-    void* d_trace = nullptr;
-    size_t trace_bytes = 0;
-    WavefrontScratch wf;
-    float* d_part = nullptr;   // partial sums of the sample chunks (render_mega)
-    size_t part_floats = 0;
-    bool pending = false;
-    cudaStream_t pending_stream = nullptr;
-};
+}  // namespace rtb
 
 static int check_device() {
     int n = 0;
@@ -87,7 +38,7 @@ static int check_device() {
 
 extern "C" {
 
-const char* rt_last_error(void) { return g_err.c_str(); }
+const char* rt_last_error(void) { return last_error().c_str(); }
 const char* rt_version(void) { return "rt_b200 0.1 (sm_100a)"; }
 int rt_device_count(void) {
     int n = 0;
@@ -228,7 +179,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
     auto chk2 = [&](cudaError_t e) { if (e != cudaSuccess) { cudaGetLastError(); fail(RT_ERR_CUDA, cudaGetErrorString(e)); return 1; } return 0; };
     if (chk2(cudaMalloc((void**)&s->d_tile_counter, 64)) || chk2(cudaMalloc((void**)&s->d_counters, 64)) ||
         chk2(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) || chk2(cudaEventCreate(&s->ev0)) ||
-        chk2(cudaEventCreate(&s->ev1)))
+        chk2(cudaEventCreate(&s->ev1)) || chk2(cudaEventCreate(&s->ev2)))
         return bail(RT_ERR_CUDA);
     auto t2 = std::chrono::steady_clock::now();
 
@@ -277,6 +228,7 @@ int rt_scene_rebuild(rt_scene* s, const void* spheres, int S, const void* planes
         if (pl[i].type < 0 || pl[i].type > 2) return fail(RT_ERR_INVALID, "rt_scene_rebuild: plane type must be QUAD/ELLIPSE/TRIANGLE");
     }
     if (s->pending) return fail(RT_ERR_INVALID, "rt_scene_rebuild: a frame is in flight (call rt_render_finish first)");
+    DeviceGuard guard(s->device);
     RT_CUDA(cudaStreamSynchronize(s->stream));
     GpuBuildResult g;
     cudaError_t ge = gpu_build_scene(sp, S, pl, P, nullptr, g);
@@ -324,15 +276,17 @@ int rt_scene_rebuild(rt_scene* s, const void* spheres, int S, const void* planes
 
 void rt_scene_destroy(rt_scene* s) {
     if (!s) return;
+    DeviceGuard guard(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
     if (s->tex_array) cudaFreeArray(s->tex_array);
     void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
-                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_part};
+                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_part, s->d_packed};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->ev2) cudaEventDestroy(s->ev2);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -344,31 +298,70 @@ int rt_scene_get_stats(const rt_scene* s, rt_scene_stats* out) {
     return RT_OK;
 }
 
-static rt_render_opts resolve_opts(const rt_render_opts* in) {
+}  // extern "C"
+
+namespace rtb {
+
+static void default_opts(rt_render_opts& d) {
+    memset(&d, 0, sizeof d);
+    d.tex_mode = RT_TEX_GPU;
+    d.top_nodes_in_smem = -1;
+    d.tile_nranks = 1;
+    d.sample_chunk = 0;
+}
+
+// struct_size says how much of the struct the caller knows: fields beyond it (a caller compiled against an older header)
+// and everything when it is <= 0 (a zero-initialised struct) take the defaults
+rt_render_opts resolve_opts(const rt_render_opts* in) {
     rt_render_opts o;
-    memset(&o, 0, sizeof o);
-    o.tex_mode = RT_TEX_GPU;
-    o.top_nodes_in_smem = -1;
-    o.tile_nranks = 1;
-    o.sample_chunk = 0;
-    if (in) {
-        size_t n = in->struct_size > 0 && (size_t)in->struct_size < sizeof o ? (size_t)in->struct_size : sizeof o;
+    default_opts(o);
+    if (in && in->struct_size > 0) {
+        size_t n = (size_t)in->struct_size < sizeof o ? (size_t)in->struct_size : sizeof o;
+        rt_render_opts d = o;
         memcpy(&o, in, n);
-        if (n < sizeof o) {  // fields beyond the caller's struct keep their defaults
-            rt_render_opts d;
-            memset(&d, 0, sizeof d);
-            d.tex_mode = RT_TEX_GPU;
-            d.top_nodes_in_smem = -1;
-            d.tile_nranks = 1;
-            d.sample_chunk = 0;
-            memcpy((char*)&o + n, (char*)&d + n, sizeof o - n);
-        }
+        if (n < sizeof o) memcpy((char*)&o + n, (char*)&d + n, sizeof o - n);
     }
     if (o.tile_nranks < 1) o.tile_nranks = 1;
     return o;
 }
 
-static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, float* d_fb, cudaStream_t stream) {
+int ensure_framebuffer(rt_scene* s, size_t n) {
+    if (s->fb_floats < n) {
+        if (s->d_fb) cudaFree(s->d_fb);
+        s->d_fb = nullptr;
+        s->fb_floats = 0;
+        RT_CUDA(cudaMalloc((void**)&s->d_fb, n * sizeof(float)));
+        s->fb_floats = n;
+    }
+    return RT_OK;
+}
+
+// Sample chunks of the megakernel (kernels.h, FrameParams): sizes shrink geometrically -- each chunk takes `keep` of what is
+// left -- down to `last` samples, at most kMaxChunks of them.  chunk 0 accumulates in the framebuffer; every further chunk
+// needs one scratch plane of W*H*3 floats.  Returns the number of chunks and fills start[0..n].
+static int plan_chunks(int spp, int last, int max_chunks, int* start) {
+    double keep = 2.0 / 3.0;
+    if (const char* e = getenv("RTB_CHUNK_KEEP")) keep = atof(e);
+    if (!(keep >= 0.25 && keep <= 0.9)) keep = 2.0 / 3.0;
+    if (last < 1) last = 1;
+    int n = 0, done = 0;
+    start[0] = 0;
+    while (done < spp) {
+        int left = spp - done, take;
+        if (n + 1 >= max_chunks || left <= last) take = left;
+        else {
+            take = (int)(left * keep + 0.5);
+            if (take < last) take = last;
+            if (left - take < last) take = left - last;  // never leave a remainder shorter than the last chunk
+            if (take < 1) take = left;
+        }
+        done += take;
+        start[++n] = done;
+    }
+    return n;
+}
+
+int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, float* d_fb, cudaStream_t stream) {
     if (!s || !cam76 || !d_fb) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
     rt_render_opts o = resolve_opts(opts_in);
     FrameParams fp;
@@ -384,37 +377,47 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     fp.tiles_x = (fp.cam.W + kTile - 1) / kTile;
     fp.tiles_y = (fp.cam.H + kTile - 1) / kTile;
     int tiles = fp.tiles_x * fp.tiles_y;
-    fp.my_tiles = tiles > o.tile_rank ? (tiles - o.tile_rank + o.tile_nranks - 1) / o.tile_nranks : 0;
+    fp.my_tiles = (tiles + o.tile_nranks - 1) / o.tile_nranks;  // groups of the interleave; a rank's slot in the last one may be empty
     fp.fb = d_fb;
     fp.tile_counter = s->d_tile_counter;
     fp.counters = s->d_counters;
     // sample chunks: shorter work items at the end of the frame (the tail is what limits strong scaling over GPUs).
     // Only the production stream is chunked: parity mode keeps the reference's per-pixel summation order bit for bit.
     fp.part = nullptr;
-    fp.chunk_spp = fp.cam.spp > 0 ? fp.cam.spp : 1;
     fp.nchunks = 1;
-    int want_chunk = o.sample_chunk;
+    fp.chunk_start[0] = 0;
+    fp.chunk_start[1] = fp.cam.spp;
+    int want_chunk = o.sample_chunk;   // > 0: length of the LAST chunk(s); 0: auto; < 0: never split
     if (o.rng != RT_RNG_PHILOX) want_chunk = -1;
     if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 2 : -1;
     if (want_chunk > 0 && o.kernel == RT_KERNEL_MEGA && fp.cam.spp > want_chunk && fp.cam.depth > 0) {
-        int n = (fp.cam.spp + want_chunk - 1) / want_chunk;
-        // the partial-sum planes are capped at 128 chunks and ~3.3 GB (128 planes of a 1080p frame, 8 of an 8K frame)
-        size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
-        int cap = (int)((size_t)3300000000ull / plane_bytes);
-        if (cap > 128) cap = 128;
-        if (cap < 1) cap = 1;
-        if (n > cap) n = cap;
-        fp.chunk_spp = (fp.cam.spp + n - 1) / n;
-        fp.nchunks = (fp.cam.spp + fp.chunk_spp - 1) / fp.chunk_spp;
-        size_t need = (size_t)fp.nchunks * fp.cam.W * fp.cam.H * 3;
-        if (s->part_floats < need) {
+        // scratch: one plane per chunk after the first, at most a quarter of the free device memory and never more than 1 GiB
+        // (6 planes of a 1080p frame are 149 MB; an 8K frame gets 2); if the allocation fails the frame renders with fewer
+        // chunks, in the end unsplit -- a longer tail, the same samples
+        const size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
+        int max_chunks = 6;
+        if (const char* e = getenv("RTB_MAX_CHUNKS")) max_chunks = atoi(e);
+        if (max_chunks > kMaxChunks) max_chunks = kMaxChunks;
+        if (max_chunks < 1) max_chunks = 1;
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); free_b = 0; }
+        size_t budget = (free_b + s->part_floats * sizeof(float)) / 4;
+        if (budget > ((size_t)1 << 30)) budget = (size_t)1 << 30;
+        while (max_chunks > 1 && (size_t)(max_chunks - 1) * plane_bytes > budget) --max_chunks;
+        for (;;) {
+            fp.nchunks = plan_chunks(fp.cam.spp, want_chunk, max_chunks, fp.chunk_start);
+            if (fp.nchunks <= 1) break;
+            const size_t need = (size_t)(fp.nchunks - 1) * fp.cam.W * fp.cam.H * 3;
+            if (s->part_floats >= need) break;
             if (s->d_part) cudaFree(s->d_part);
             s->d_part = nullptr;
             s->part_floats = 0;
-            RT_CUDA(cudaMalloc((void**)&s->d_part, need * sizeof(float)));
-            s->part_floats = need;
+            if (cudaMalloc((void**)&s->d_part, need * sizeof(float)) == cudaSuccess) { s->part_floats = need; break; }
+            cudaGetLastError();
+            max_chunks = fp.nchunks - 1;  // out of memory: try with one plane less
         }
-        fp.part = s->d_part;
+        if (fp.nchunks > 1) fp.part = s->d_part;
+        else { fp.nchunks = 1; fp.chunk_start[0] = 0; fp.chunk_start[1] = fp.cam.spp; }
     }
     DevScene dev = s->dev;
     // megakernel default: no staging (measured no gain); the other kernels keep the 64-node default
@@ -438,16 +441,21 @@ static int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* op
     if (o.kernel == RT_KERNEL_MEGA) RT_CUDA(launch_render_mega(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else if (o.kernel == RT_KERNEL_POOL) RT_CUDA(launch_render_pool(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else RT_CUDA(launch_render_wavefront(dev, fp, o.rng, o.exact_math, o.count_work, cfg, s->wf, stream));
-    if (fp.nchunks > 1) RT_CUDA(launch_reduce_chunks(fp, stream));
+    if (fp.nchunks > 1) RT_CUDA(launch_reduce_chunks(fp, s->num_sms, stream));
     RT_CUDA(cudaEventRecord(s->ev1, stream));
     s->pending = true;
     s->pending_stream = stream;
     return RT_OK;
 }
 
+}  // namespace rtb
+
+extern "C" {
+
 int rt_render_finish(rt_scene* s, unsigned long long* segs, float* kernel_ms, rt_work_counters* counters) {
     if (!s) return fail(RT_ERR_INVALID, "rt_render_finish: NULL scene");
     if (!s->pending) return fail(RT_ERR_INVALID, "rt_render_finish: no frame in flight");
+    DeviceGuard guard(s->device);
     RT_CUDA(cudaEventSynchronize(s->ev1));
     s->pending = false;
     unsigned long long c[8];
@@ -463,6 +471,8 @@ int rt_render_finish(rt_scene* s, unsigned long long* segs, float* kernel_ms, rt
 }
 
 int rt_render_device(rt_scene* s, const void* cam76, const rt_render_opts* opts, void* d_fb, void* cuda_stream) {
+    if (!s) return fail(RT_ERR_INVALID, "rt_render_device: NULL scene");
+    DeviceGuard guard(s->device);
     return launch_frame(s, cam76, opts, (float*)d_fb, (cudaStream_t)cuda_stream);
 }
 
@@ -472,17 +482,13 @@ int rt_render(rt_scene* s, const void* cam76, const rt_render_opts* opts, float*
     CameraPod cam;
     memcpy(&cam, cam76, sizeof cam);
     if (cam.W <= 0 || cam.H <= 0) return fail(RT_ERR_INVALID, "rt_render: bad CameraData");
+    DeviceGuard guard(s->device);
     size_t n = (size_t)cam.W * cam.H * 3;
-    if (s->fb_floats < n) {
-        if (s->d_fb) cudaFree(s->d_fb);
-        s->d_fb = nullptr;
-        s->fb_floats = 0;
-        RT_CUDA(cudaMalloc((void**)&s->d_fb, n * sizeof(float)));
-        s->fb_floats = n;
-    }
+    int rc = ensure_framebuffer(s, n);
+    if (rc) return rc;
     rt_render_opts o = resolve_opts(opts);
     if (o.tile_nranks > 1) RT_CUDA(cudaMemsetAsync(s->d_fb, 0, n * sizeof(float), s->stream));
-    int rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
+    rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
     if (rc) return rc;
     RT_CUDA(cudaMemcpyAsync(fb, s->d_fb, n * sizeof(float), cudaMemcpyDeviceToHost, s->stream));
     rc = rt_render_finish(s, segs, kernel_ms, counters);
@@ -498,26 +504,26 @@ int rt_render_u8(rt_scene* s, const void* cam76, const rt_render_opts* opts, int
     CameraPod cam;
     memcpy(&cam, cam76, sizeof cam);
     if (cam.W <= 0 || cam.H <= 0) return fail(RT_ERR_INVALID, "rt_render_u8: bad CameraData");
+    DeviceGuard guard(s->device);
     size_t n = (size_t)cam.W * cam.H * 3;
-    if (s->fb_floats < n) {
-        if (s->d_fb) cudaFree(s->d_fb);
-        s->d_fb = nullptr;
-        s->fb_floats = 0;
-        RT_CUDA(cudaMalloc((void**)&s->d_fb, n * sizeof(float)));
-        s->fb_floats = n;
-    }
+    int rc = ensure_framebuffer(s, n);
+    if (rc) return rc;
     rt_render_opts o = resolve_opts(opts);
     if (o.tile_nranks > 1) RT_CUDA(cudaMemsetAsync(s->d_fb, 0, n * sizeof(float), s->stream));
-    int rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
+    rc = launch_frame(s, cam76, opts, s->d_fb, s->stream);
     if (rc) return rc;
     rc = rt_render_finish(s, segs, kernel_ms, nullptr);
     if (rc) return rc;
     return rt_tonemap_u8(s, nullptr, cam.W, cam.H, divisor, rgb);
 }
 
-int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float tmax, int* type, int* index, float* t) {
+int rt_trace_primary_ex(rt_scene* s, const float* rays6, int n, float tmin, float tmax, const rt_trace_opts* topts, int* type,
+                        int* index, float* t) {
     if (!s || (n > 0 && (!rays6 || !type || !index || !t)) || n < 0) return fail(RT_ERR_INVALID, "rt_trace_primary: bad argument");
+    int exact = 1;
+    if (topts && topts->struct_size >= (int)(2 * sizeof(int))) exact = topts->exact_math ? 1 : 0;
     if (n == 0) return RT_OK;
+    DeviceGuard guard(s->device);
     size_t need = (size_t)n * (6 * 4 + 4 + 4 + 4);
     if (s->trace_bytes < need) {
         if (s->d_trace) cudaFree(s->d_trace);
@@ -532,7 +538,8 @@ int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float t
     float* d_t = (float*)(d_index + n);
     RT_CUDA(cudaMemcpyAsync(d_rays, rays6, (size_t)n * 24, cudaMemcpyHostToDevice, s->stream));
     DevScene dev = s->dev;
-    RT_CUDA(launch_trace_primary(dev, d_rays, n, tmin, tmax, d_type, d_index, d_t, s->stream));
+    if (!exact) dev.top_nodes = 0;  // as the production megakernel launches: every node through the L1 (__ldg), nothing staged
+    RT_CUDA(launch_trace_primary(dev, d_rays, n, tmin, tmax, exact, d_type, d_index, d_t, s->num_sms, s->stream));
     RT_CUDA(cudaMemcpyAsync(type, d_type, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
     RT_CUDA(cudaMemcpyAsync(index, d_index, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
     RT_CUDA(cudaMemcpyAsync(t, d_t, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
@@ -540,10 +547,15 @@ int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float t
     return RT_OK;
 }
 
+int rt_trace_primary(rt_scene* s, const float* rays6, int n, float tmin, float tmax, int* type, int* index, float* t) {
+    return rt_trace_primary_ex(s, rays6, n, tmin, tmax, nullptr, type, index, t);
+}
+
 int rt_tonemap_u8(rt_scene* s, const void* d_fb, int W, int H, int divisor, unsigned char* rgb) {
     if (!s || !rgb || W <= 0 || H <= 0 || divisor <= 0) return fail(RT_ERR_INVALID, "rt_tonemap_u8: bad argument");
     const float* src = d_fb ? (const float*)d_fb : s->d_fb;
     if (!src) return fail(RT_ERR_INVALID, "rt_tonemap_u8: no framebuffer");
+    DeviceGuard guard(s->device);
     size_t n = (size_t)W * H * 3;
     if (s->u8_bytes < n) {
         if (s->d_u8) cudaFree(s->d_u8);
@@ -552,7 +564,7 @@ int rt_tonemap_u8(rt_scene* s, const void* d_fb, int W, int H, int divisor, unsi
         RT_CUDA(cudaMalloc((void**)&s->d_u8, n));
         s->u8_bytes = n;
     }
-    RT_CUDA(launch_tonemap(src, n, divisor, s->d_u8, s->stream));
+    RT_CUDA(launch_tonemap(src, n, divisor, s->d_u8, s->num_sms, s->stream));
     RT_CUDA(cudaMemcpyAsync(rgb, s->d_u8, n, cudaMemcpyDeviceToHost, s->stream));
     RT_CUDA(cudaStreamSynchronize(s->stream));
     return RT_OK;
@@ -561,13 +573,21 @@ int rt_tonemap_u8(rt_scene* s, const void* d_fb, int W, int H, int divisor, unsi
 unsigned long long rt_tiles_packed_floats(int W, int H, int nranks) { return tiles_packed_floats(W, H, nranks < 1 ? 1 : nranks); }
 int rt_tiles_pack(rt_scene* s, const void* d_fb, int W, int H, int rank, int nranks, void* d_packed, void* stream) {
     if (!s || !d_fb || !d_packed || nranks < 1 || rank < 0 || rank >= nranks) return fail(RT_ERR_INVALID, "rt_tiles_pack: bad argument");
-    RT_CUDA(launch_tiles_pack((const float*)d_fb, W, H, rank, nranks, (float*)d_packed, (cudaStream_t)stream));
+    DeviceGuard guard(s->device);
+    RT_CUDA(launch_tiles_pack((const float*)d_fb, W, H, rank, nranks, (float*)d_packed, s->num_sms, (cudaStream_t)stream));
     return RT_OK;
 }
 int rt_tiles_unpack(rt_scene* s, const void* d_all, int W, int H, int nranks, void* d_fb, void* stream) {
     if (!s || !d_fb || !d_all || nranks < 1) return fail(RT_ERR_INVALID, "rt_tiles_unpack: bad argument");
-    RT_CUDA(launch_tiles_unpack((const float*)d_all, W, H, nranks, (float*)d_fb, (cudaStream_t)stream));
+    DeviceGuard guard(s->device);
+    RT_CUDA(launch_tiles_unpack((const float*)d_all, W, H, nranks, -1, (float*)d_fb, s->num_sms, (cudaStream_t)stream));
     return RT_OK;
+}
+void rt_tile_owner(int tile, int nranks, int* rank, int* k) {
+    int r = 0, kk = tile;
+    if (nranks > 1) tile_owner(tile, nranks, r, kk);
+    if (rank) *rank = r;
+    if (k) *k = kk;
 }
 
 }  // extern "C"

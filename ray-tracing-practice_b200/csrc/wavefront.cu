@@ -30,7 +30,7 @@ struct WfState {
 };
 
 __device__ __forceinline__ bool slot_pixel(const FrameParams& fp, int slot, int& x, int& y) {
-    int tile = (slot >> 8) * fp.tile_nranks + fp.tile_rank, q = slot & 255, blk = q >> 5;
+    int tile = tile_of_rank(slot >> 8, fp.tile_rank, fp.tile_nranks), q = slot & 255, blk = q >> 5;
     x = (tile % fp.tiles_x) * kTile + (blk & 1) * 8 + (q & 7);
     y = (tile / fp.tiles_x) * kTile + (blk >> 1) * 4 + ((q >> 3) & 3);
     return x < fp.cam.W && y < fp.cam.H;

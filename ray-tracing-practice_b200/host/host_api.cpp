@@ -104,6 +104,20 @@ int rth_gpu_render(void* hh, int format, char* log, int log_cap) {
     if (log && log_cap > 0) { std::strncpy(log, os.str().c_str(), log_cap - 1); log[log_cap - 1] = 0; }
     return rc;
 }
+// flags: 1 parity, 2 no pipeline, 4 split tiles
+int rth_gpu_render_ex(void* hh, int format, int flags, int num_gpus, char* log, int log_cap) {
+    HostHandle* h = (HostHandle*)hh;
+    std::ostringstream os;
+    DriverOpts d;
+    d.format = format;
+    d.num_gpus = num_gpus;
+    d.parity = flags & 1;
+    d.pipeline = !(flags & 2);
+    d.split_tiles = flags & 4;
+    int rc = gpu_render(h->params, h->scene, d, os);
+    if (log && log_cap > 0) { std::strncpy(log, os.str().c_str(), log_cap - 1); log[log_cap - 1] = 0; }
+    return rc;
+}
 void rth_set_output(void* hh, const char* pattern, int num_frames, int W, int H, int max_depth, int sqrt_spp) {
     HostHandle* h = (HostHandle*)hh;
     if (pattern) h->params.output_path = pattern;

@@ -99,5 +99,13 @@ bool load_texels(const std::string& path, std::vector<float>& rgba, int& w, int&
 // num_gpus > 1 distributes the (independent) frames over that many devices of the box, frame n on device n % num_gpus;
 // 0 = take RTB_GPUS from the environment, default 1.
 int gpu_render(const SceneParams& p, const HostScene& scene, int format, std::ostream& log, int num_gpus = 0);
+struct DriverOpts {
+    int format = 0;            // 0 binary, 1 png, 2 text ppm
+    int num_gpus = 0;          // 0: RTB_GPUS or 1
+    bool parity = false;       // RT_RNG_REFERENCE + exact math + CPU texture semantics: the reference program's own frames, byte for byte
+    bool pipeline = true;      // false: write each file before the next frame starts (the reference's strictly serial loop)
+    bool split_tiles = false;  // with num_gpus > 1: all devices render EVERY frame together (rt_render_tiles) instead of a frame each
+};
+int gpu_render(const SceneParams& p, const HostScene& scene, const DriverOpts& opts, std::ostream& log);
 
 }  // namespace rtb

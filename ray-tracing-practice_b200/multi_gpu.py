@@ -1,10 +1,12 @@
 """Multi-GPU frame: interleaved 16x16 tiles, one process per GPU, gather of the packed tiles to rank 0.
 
 The reference is single-GPU; this is the B200-native extension BASELINE.json asks for.  Pixels
-are independent and the scene is read-only, so every rank holds the whole scene and renders the tiles t with
-t % world == rank (rt_render_device with tile_rank / tile_nranks).  The only exchange is the end-of-frame gather of
-W*H*12/world bytes per rank to rank 0 (torch.distributed.gather -> NCCL send/recv over NVLink), followed by an
-unpack kernel (rt_tiles_unpack).  The numpy pack / unpack below state the same tile layout for the CPU (gloo) tests.
+are independent and the scene is read-only, so every rank holds the whole scene and renders its share of the tiles
+(rt_render_tiles; tiles are dealt in groups of `world` consecutive ids, the position inside a group rotated by a hash
+of the group -- include/rt_b200.h, rt_tile_owner).  The only exchange is the end-of-frame gather of W*H*12/world
+bytes per rank to rank 0 (grouped ncclSend / ncclRecv inside rt_render_tiles), followed by an unpack kernel.  The numpy
+pack / unpack below state the same tile layout for the CPU (gloo) tests; TiledFrame is the same frame assembled with
+torch.distributed instead of the library's own communicator.
 """
 import numpy as np
 
@@ -21,12 +23,29 @@ def packed_floats(W, H, world):
     return per * TILE * TILE * 3
 
 
+def tile_rot(g, world):
+    """position rotation of tile group g (kernels.h: tile_rot)"""
+    return (((g * 0x9E3779B1) & 0xFFFFFFFF) >> 16) % world if world > 1 else 0
+
+
+def tile_of_rank(k, rank, world):
+    return k * world + (rank - tile_rot(k, world)) % world
+
+
+def tile_owner(t, world):
+    k = t // world
+    return (t % world + tile_rot(k, world)) % world, k
+
+
 def pack_tiles_np(fb, rank, world):
-    """numpy statement of rt_tiles_pack: rank's tiles in increasing tile id, 16x16x3 floats each, zero padded."""
+    """numpy statement of rt_tiles_pack: rank's tiles in increasing k, 16x16x3 floats each, zero padded."""
     H, W = fb.shape[:2]
     tx, ty = tile_grid(W, H)
     out = np.zeros(packed_floats(W, H, world), np.float32).reshape(-1, TILE, TILE, 3)
-    for k, t in enumerate(range(rank, tx * ty, world)):
+    for k in range((tx * ty + world - 1) // world):
+        t = tile_of_rank(k, rank, world)
+        if t >= tx * ty:
+            continue
         x0, y0 = (t % tx) * TILE, (t // tx) * TILE
         blk = fb[y0:y0 + TILE, x0:x0 + TILE]
         out[k, :blk.shape[0], :blk.shape[1]] = blk
@@ -39,7 +58,7 @@ def unpack_tiles_np(packed_all, W, H, world):
     per = packed_floats(W, H, world)
     fb = np.zeros((H, W, 3), np.float32)
     for t in range(tx * ty):
-        r, k = t % world, t // world
+        r, k = tile_owner(t, world)
         blk = packed_all[r * per:(r + 1) * per].reshape(-1, TILE, TILE, 3)[k]
         x0, y0 = (t % tx) * TILE, (t // tx) * TILE
         h, w = min(TILE, H - y0), min(TILE, W - x0)

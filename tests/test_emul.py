@@ -48,6 +48,17 @@ def test_reference_stream_render_is_bit_identical(emul, EmuSceneCls, rt):
     assert cnt[0] == int(g["segments"][0]) and fb.tobytes() == g["fb_sum"].tobytes()
 
 
+def test_textured_spheres_render_is_bit_identical(emul, EmuSceneCls):
+    """sphere_uv (shade.cuh) feeding the CPU-semantics texture lookup: the device code's exact policy, run on the host,
+    reproduces the reference frame of a scene whose textured material sits on spheres"""
+    g = golden("textured_spheres.npz")
+    es = EmuSceneCls(emul, g["spheres"], g["planes"], g["materials"], g["tex"], int(g["tex_mat"][0]))
+    fb, cnt = es.render(g["camera"], rng=1, exact=1, tex_mode=0)
+    assert cnt[0] == int(g["segments"][0])
+    same = (bits(fb) == bits(g["fb_sum"])).all(-1)
+    assert same.mean() == 1.0, same.mean()
+
+
 def test_philox_estimator_agrees_in_expectation(emul, EmuSceneCls, orc, rt):
     """production stream (Philox, direct sampling, fast math): same estimator => same image in expectation"""
     hs = rt.synthetic_scene(500, W=64, H=36, sqrt_spp=12, depth=8, seed=5)

@@ -1,0 +1,372 @@
+"""north_star's correctness gates on the PRODUCTION path (fast fp32 + SFU approximations + Philox -- the configuration whose
+Mrays/s bench.py reports), at BASELINE.json's scene sizes, against the oracle and against the reference's OWN CUDA render
+(oracle/_ref: the unmodified render_kernel of src/camera.cu:17-34 built for sm_100).  All calls go through the C-ABI.
+Run on the B200 box: pytest -m gpu."""
+import threading
+
+import numpy as np
+import pytest
+from conftest import bits, golden
+
+pytestmark = pytest.mark.gpu
+
+# ---- stated budgets (north_star: ids bit-exact, t within 1e-5 relative; mismatch classes documented)
+MAX_REL_T = 1e-5            # on rays whose ids agree
+ID_BUDGET_FAST = 1e-5       # fraction of rays whose production-arithmetic id may differ from the reference's BVH walk ...
+ID_BUDGET_REFWALK = 2e-4    # ... and from it in exact mode: the reference's own slab test culls grazing hits its leaf test accepts
+NEAR_TIE_REL = 1e-4         # a mismatch is a "near tie" when the two hits' t agree to this
+
+
+def _classify(rays, ty, ix, t, oy, oi, orec, sp):
+    """every id mismatch must be one of: near tie (two primitives at the same distance within NEAR_TIE_REL), or a grazing
+    sphere hit (tangent within fp32 rounding: discriminant <= 1e-3 of hb^2) on either side.  Returns (n_tie, n_graze, n_other)"""
+    bad = np.nonzero((ty != oy) | (ix != oi))[0]
+    tie = graze = other = 0
+    for i in bad:
+        ta, tb = float(t[i]), float(orec[i, 0])
+        if ty[i] >= 0 and oy[i] >= 0 and abs(ta - tb) <= NEAR_TIE_REL * max(ta, tb):
+            tie += 1
+            continue
+        is_graze = False
+        for typ, idx in ((ty[i], ix[i]), (oy[i], oi[i])):
+            if typ == 0:
+                o, d = rays[i, :3].astype(np.float64), rays[i, 3:].astype(np.float64)
+                oc = o - sp["center"][idx].astype(np.float64)
+                hb, a, c = oc @ d, d @ d, oc @ oc - float(sp["radius"][idx]) ** 2
+                if hb * hb - a * c <= 1e-3 * hb * hb:
+                    is_graze = True
+        graze += is_graze
+        other += not is_graze
+        print("  mismatch ray %d: gpu (%d,%d,t=%.9g) oracle (%d,%d,t=%.9g) rel dt %.3g %s" % (
+            i, ty[i], ix[i], ta, oy[i], oi[i], tb, abs(ta - tb) / max(abs(tb), 1e-30), "grazing" if is_graze else "UNEXPLAINED"))
+    return tie, graze, other
+
+
+@pytest.mark.parametrize("n", [10000, 100000, 1000000])
+def test_production_and_exact_ids_t_full_1080p(rt, orc, n):
+    """ALL 1920x1080 pixel-centre rays of the BASELINE scene with n spheres (configs[1], [2]; [3]'s 1M-sphere deep BVH):
+    (a) rt_trace_primary_ex(exact_math=0) -- the arithmetic render_mega<.., fast, ..> shades with -- and (b) exact mode, each
+    vs the oracle's id-recording walk of the REFERENCE BVH (include/bvh.h:19-65 over include/bvh_builder.h's tree) on all
+    rays and vs the exhaustive scan of the reference leaf tests on a >= 10 000-ray sample."""
+    hs = rt.synthetic_scene(n, W=1920, H=1080, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    sc = rt.Scene(sp, pl, mt)
+    rays = rt.pixel_center_rays(hs.camera(0))
+    assert len(rays) == 1920 * 1080
+    osc = orc.scene(sp, pl, mt)
+    by, bi, brec = osc.trace(rays, 1)
+    sel = np.arange(0, len(rays), 199)
+    assert len(sel) >= 10000
+    ly, li, lrec = osc.trace(rays[sel], 0)
+    for exact in (True, False):
+        ty, ix, t = sc.trace_primary(rays, exact=exact)
+        name = "exact" if exact else "production"
+        # ---- vs the exhaustive scan (the reference's leaf tests over all primitives)
+        mism_lin = (ty[sel] != ly) | (ix[sel] != li)
+        ok = ~mism_lin & (ly >= 0)
+        rel = np.abs(t[sel][ok] - lrec[ok, 0]) / lrec[ok, 0]
+        print("n=%d %s: vs linear scan %d / %d ids differ, max rel dt %.3g; " % (n, name, mism_lin.sum(), len(sel), rel.max()), end="")
+        if exact:
+            assert mism_lin.sum() == 0
+            assert (bits(t[sel][ok]) == bits(lrec[ok, 0])).all()       # bit-equal t
+        else:
+            tie, graze, other = _classify(rays[sel], ty[sel], ix[sel], t[sel], ly, li, lrec, sp)
+            assert other == 0 and mism_lin.mean() <= 1e-3              # (one ray of the sample is 1e-4)
+        assert rel.max() <= MAX_REL_T
+        # ---- vs the reference's BVH walk, every ray
+        mism = (ty != by) | (ix != bi)
+        ok = ~mism & (by >= 0)
+        rel = np.abs(t[ok] - brec[ok, 0]) / brec[ok, 0]
+        tie, graze, other = _classify(rays, ty, ix, t, by, bi, brec, sp)
+        print("vs reference BVH walk %d / %d ids differ (%d near ties, %d grazing, %d unexplained), max rel dt %.3g, hit rate %.3f"
+              % (mism.sum(), len(rays), tie, graze, other, rel.max(), (ty >= 0).mean()))
+        assert other == 0
+        assert mism.mean() <= (ID_BUDGET_REFWALK if exact else max(ID_BUDGET_FAST, ID_BUDGET_REFWALK))
+        if not exact:
+            # production vs exact mode of the same library: the rays the fast arithmetic itself changes
+            ey, ei, et = sc.trace_primary(rays, exact=True)
+            d = (ty != ey) | (ix != ei)
+            print("    production vs exact mode: %d / %d ids differ (%.2e)" % (d.sum(), len(rays), d.mean()))
+            assert d.mean() <= ID_BUDGET_FAST
+        assert rel.max() <= MAX_REL_T
+    sc.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+def _psnr(a, b, peak):
+    return 10 * np.log10(peak ** 2 / np.mean((np.minimum(a, peak) - np.minimum(b, peak)) ** 2))
+
+
+def _image_gate(rt, ref, sp, pl, mt, tex, cam, spp, tag, psnr_floor):
+    """production render (Philox, fast math, texture unit) vs the reference's own CUDA render of the same arrays.
+    Gates on the MEAN image (sum / spp): per-channel MAE <= 1.25 x the MAE between two independently seeded production
+    renders (the Monte-Carlo noise floor), image mean within 1 %, PSNR >= psnr_floor dB (peak = the 99.9th percentile of the
+    reference image; light sources clip), and a signed-bias test per first-hit material class:
+    |mean(repo - ref)| <= 4 sigma/sqrt(N) with sigma from the two production renders."""
+    from oracle import oracle_py as O
+    sc = rt.Scene(sp, pl, mt, tex, 0 if tex is not None else -1)
+    rs = ref.scene(sp, pl, mt, tex, 0 if tex is not None else -1)
+    fr, ms = O.gpu_render_ref(rs, cam, reps=1)                      # the reference's render_kernel on this GPU
+    fa, ia = sc.render(cam, seed=21)
+    fb_, ib = sc.render(cam, seed=22)
+    ma, mb, mr = fa / spp, fb_ / spp, fr / spp
+    noise = np.abs(ma - mb).mean(axis=(0, 1))
+    mae = np.abs(ma - mr).mean(axis=(0, 1))
+    peak = float(np.percentile(mr, 99.9))
+    psnr, psnr_self = _psnr(ma, mr, peak), _psnr(ma, mb, peak)
+    print("%s: MAE vs reference CUDA render %s, noise floor %s, PSNR %.2f dB (two production renders: %.2f dB), means %.6f / %.6f, "
+          "reference kernel %.1f ms, ours %.2f ms" % (tag, mae, noise, psnr, psnr_self, ma.mean(), mr.mean(), ms, ia["kernel_ms"]))
+    assert (mae <= 1.25 * noise + 1e-4).all()
+    assert abs(ma.mean() - mr.mean()) <= 0.01 * mr.mean()
+    assert psnr >= psnr_floor and psnr >= psnr_self - 1.0
+    # signed bias per class of first hit (pixel-centre ray): glass / metal / textured floor / the rest
+    ty, ix, _ = sc.trace_primary(rt.pixel_center_rays(cam))
+    mat = np.full(len(ty), -1)
+    mat[ty == 0] = sp["material_idx"][ix[ty == 0]]
+    mat[ty == 1] = pl["material_idx"][ix[ty == 1]]
+    mtype = np.where(mat >= 0, mt["type"][np.clip(mat, 0, len(mt) - 1)], -1)
+    cls = np.where(mat == 0, 10, mtype).reshape(ma.shape[:2])      # material 0 is the floor (create_scene, src/main.cu:346-426)
+    lum_d, lum_n = (ma - mr).mean(-1), (ma - mb).mean(-1)
+    for c, name in ((10, "floor"), (0, "lambertian"), (1, "metal"), (2, "glass"), (-1, "miss")):
+        m = cls == c
+        if m.sum() < 400:
+            continue
+        sigma = lum_n[m].std() + 1e-12
+        z = lum_d[m].mean() / (sigma / np.sqrt(m.sum()))
+        print("    %-10s %7d px  mean diff %+.3e  z = %+.2f" % (name, m.sum(), lum_d[m].mean(), z))
+        assert abs(z) <= 4.0, (name, z)
+    sc.close()
+
+
+def test_image_vs_reference_cuda_render_shipped_scene_textured(rt, ref):
+    """configs[0]: the reference's shipped scene (94 spheres + 105 planes, glass solids, depth 50) WITH a floor texture of
+    floor.jpg's shape through the texture unit (RT_TEX_GPU), 1024 spp at 270x180."""
+    hs = rt.HostScene(rt.shipped_config_text(W=270, H=180, sqrt_spp=32, max_depth=50), texture="")
+    sp, pl, mt, _ = hs.arrays()
+    _image_gate(rt, ref, sp, pl, mt, rt.synthetic_texture(), hs.camera(0), 1024, "shipped scene, textured", psnr_floor=30.0)
+
+
+def test_image_vs_reference_cuda_render_10k(rt, ref):
+    """configs[1]'s scene (10k spheres, depth 16) at 480x270, 1024 spp"""
+    hs = rt.synthetic_scene(10000, W=480, H=270, sqrt_spp=32, depth=16, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    _image_gate(rt, ref, sp, pl, mt, None, hs.camera(0), 1024, "10k spheres", psnr_floor=30.0)
+
+
+def _quad_scene(rt):
+    """a textured Lambertian quad seen head-on inside a huge emissive sphere: every sample's radiance is exactly the texture
+    value at its hit point (one bounce off the quad, then the light), so a 1-spp frame IS a picture of the texture filter"""
+    pl = rt.make_planes([[-2, -1.5, -3]], [[4, 0, 0]], [[0, 3, 0]], 0, rt.QUAD)
+    sp = np.zeros(1, rt.SPHERE)
+    sp["center"], sp["radius"], sp["material_idx"] = [[0, 0, 0]], 1000.0, 1
+    mt = np.zeros(2, rt.MATERIAL)
+    mt["type"] = [rt.LAMBERTIAN, rt.DIFFUSE_LIGHT]
+    mt["albedo"][0] = [1, 1, 1]
+    mt["emit"][1] = [1, 1, 1]
+    rng = np.random.default_rng(5)
+    tex = np.ones((48, 64, 4), np.float32)
+    tex[..., :3] = rng.random((48, 64, 3), dtype=np.float32)
+    cam = rt.build_camera(192, 256, [0, 0, 0], [0, 0, -3], 50.0, 1, 4)   # the quad fills the view: ~4 pixels per texel
+    return sp, pl, mt, tex, cam
+
+
+def test_texture_unit_pinned_to_reference_kernel(rt, orc, ref):
+    """the authority for texture semantics is the reference CUDA kernel's tex2D (src/camera.cu:233-236,
+    descriptor src/main.cu:24-46).  Its image of a head-on textured quad pins (1) the oracle's restatement of the hardware
+    filter (orc.tex2d mode 1: no V flip, half-texel offset, 8-bit weights) and (2) this library's RT_TEX_GPU path."""
+    from oracle import oracle_py as O
+    sp, pl, mt, tex, cam = _quad_scene(rt)
+    fr, _ = O.gpu_render_ref(ref.scene(sp, pl, mt, tex, 0), cam, reps=1)
+    assert fr.min() > 0 and fr.std() > 0.1                       # every pixel sees the quad, and the texture's contrast
+    fo, _ = orc.scene(sp, pl, mt, tex, 0).render(cam, hit_mode=1, tex_mode=1)
+    f_cpu, _ = orc.scene(sp, pl, mt, tex, 0).render(cam, hit_mode=1, tex_mode=0)
+    sc = rt.Scene(sp, pl, mt, tex, 0)
+    fg, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_GPU)
+    sc.close()
+    q = 1.0 / 256                                               # one quantum of the unit's 8-bit filter weights x texel contrast <= 1
+    for name, f in (("oracle restatement", fo), ("RT_TEX_GPU", fg)):
+        d = np.abs(f - fr)
+        print("%s vs reference kernel: max |diff| %.3g, 99th pct %.3g, mean %.3g (CPU-convention image: mean |diff| %.3g)"
+              % (name, d.max(), np.percentile(d, 99), d.mean(), np.abs(f_cpu - fr).mean()))
+        # the reference kernel contracts FMAs, so (u, v) differ from the host build's by ulps: a weight may flip by one quantum
+        assert d.max() <= 2 * q + 1e-5 and np.percentile(d, 99) <= q + 1e-5 and d.mean() <= 0.1 * q
+    assert np.abs(f_cpu - fr).mean() > 20 * np.abs(fo - fr).mean()    # and it is NOT the CPU convention (V flip, no half texel)
+
+
+def test_textured_spheres_exact_mode_matches_the_reference_frame(rt):
+    """sphere_uv (csrc/shade.cuh) on the DEVICE: the fixture's textured material sits on spheres (get_sphere_uv,
+    include/sphere.h:16-22 -> tex2D_cpu); frame of the reference's host render, from the compiled reference"""
+    g = golden("textured_spheres.npz")
+    sc = rt.Scene(g["spheres"], g["planes"], g["materials"], g["tex"], int(g["tex_mat"][0]))
+    fb, info = sc.render(g["camera"], rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    assert info["segments"] == int(g["segments"][0])
+    same = (bits(fb) == bits(g["fb_sum"])).all(-1)
+    print("textured spheres: bit-identical pixels %.6f, max |diff| %.3g" % (same.mean(), np.abs(fb - g["fb_sum"]).max()))
+    assert same.mean() >= 0.999 and np.abs(fb - g["fb_sum"]).max() <= 1e-4 * max(1.0, g["fb_sum"].max())
+    # fast mode + texture unit on spheres: same picture within Monte-Carlo noise of a 4-spp frame's mean over the image
+    fp, _ = sc.render(g["camera"], seed=3)
+    assert abs(fp.mean() - g["fb_sum"].mean()) <= 0.1 * g["fb_sum"].mean()
+    sc.close()
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+def test_scene_handle_is_usable_from_any_thread_and_device(rt):
+    """a scene lives on the device it was created on; entry points switch to it: create on the last device from
+    the main thread, render / trace / tonemap / destroy from a worker thread whose current device is 0"""
+    g = golden("test_config_frame.npz")
+    ndev = rt.device_count()
+    rt.set_device(ndev - 1)
+    sc = rt.Scene(g["spheres"], g["planes"], g["materials"])
+    want, _ = sc.render(g["camera"], seed=4)
+    rt.set_device(0)
+    out = {}
+
+    def work():
+        try:
+            rt.set_device(0)
+            a, _ = sc.render(g["camera"], seed=4)
+            ty, ix, t = sc.trace_primary(rt.pixel_center_rays(g["camera"]))
+            u8, _ = sc.render_u8(g["camera"], 2, seed=4)
+            out.update(a=a, ty=ty, u8=u8)
+        except Exception as e:  # noqa: BLE001
+            out["err"] = e
+
+    th = threading.Thread(target=work)
+    th.start()
+    th.join()
+    assert "err" not in out, out.get("err")
+    assert out["a"].tobytes() == want.tobytes() and (out["ty"] == g["type_brute"]).all()
+    assert out["u8"].tobytes() == rt.tonemap_host(want, 2).tobytes()
+    sc.close()
+
+
+def _render_tiles_threads(rt, n, sp, pl, mt, cam, **kw):
+    """n ranks as n threads of this process (rt_comm_init_all), rank i on device i % device_count"""
+    ndev = rt.device_count()
+    devs = [i % ndev for i in range(n)]
+    if len(set(devs)) < n:
+        pytest.skip("needs %d GPUs" % n)
+    comms = rt.Comm.init_all(n, devs)
+    scenes = []
+    for d in devs:
+        rt.set_device(d)
+        scenes.append(rt.Scene(sp, pl, mt))
+    rt.set_device(0)
+    res = [None] * n
+
+    def work(i):
+        try:
+            res[i] = scenes[i].render_tiles(comms[i], cam, **kw)
+        except Exception as e:  # noqa: BLE001
+            res[i] = e
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(n)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for s in scenes:
+        s.close()
+    for c in comms:
+        c.close()
+    for r in res:
+        if isinstance(r, Exception):
+            raise r
+    return res
+
+
+def test_render_tiles_single_rank_is_rt_render(rt):
+    g = golden("test_config_frame.npz")
+    sc = rt.Scene(g["spheres"], g["planes"], g["materials"])
+    want, iw = sc.render(g["camera"], seed=6)
+    got, info = sc.render_tiles(None, g["camera"], seed=6)
+    assert got.tobytes() == want.tobytes() and info["segments_total"] == iw["segments"] and info["nranks"] == 1
+    c1 = rt.Comm.init_rank(None, 0, 1)
+    got, info = sc.render_tiles(c1, g["camera"], seed=6)
+    assert got.tobytes() == want.tobytes() and info["d2h_bytes"] == want.nbytes and info["gathered_bytes"] == 0
+    none, info = sc.render_tiles(c1, g["camera"], want_host=False, seed=6)     # frame stays on the device
+    assert none is None and sc.tonemap_u8(200, 100, 2).tobytes() == rt.tonemap_host(want, 2).tobytes()
+    c1.close()
+    sc.close()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_render_tiles_over_nccl_assembles_the_single_gpu_frame(rt, n):
+    """ONE frame on n GPUs through the C-ABI: per-rank tiles, grouped ncclSend/ncclRecv to rank 0, unpack, one D2H.
+    The assembled frame is byte-identical to the single-GPU frame (pixels do not depend on who renders them)."""
+    hs = rt.synthetic_scene(2000, W=333, H=190, sqrt_spp=6, depth=8, seed=5)   # odd size: partial tiles, short last group
+    sp, pl, mt, _ = hs.arrays()
+    cam = hs.camera(0)
+    one = rt.Scene(sp, pl, mt)
+    want, iw = one.render(cam, seed=8)
+    one.close()
+    res = _render_tiles_threads(rt, n, sp, pl, mt, cam, seed=8)
+    fb0, info0 = res[0]
+    assert fb0.tobytes() == want.tobytes()
+    assert info0["segments_total"] == iw["segments"] == sum(r[1]["segments_rank"] for r in res)
+    assert all(r[0] is None for r in res[1:]) and info0["d2h_bytes"] == want.nbytes
+    per = rt.tiles_packed_floats(333, 190, n) * 4
+    assert info0["gathered_bytes"] == (n - 1) * (per + 16)
+
+
+# ------------------------------------------------------------------------------------------------------------------------
+def _program_frames_config(tmp_path, tag):
+    g = golden("program_frames.npz")
+    return str(g["config"]).replace("OUTDIR", str(tmp_path / tag)), g["frames"]
+
+
+def test_rt_main_parity_writes_the_reference_programs_frames(rt, tmp_path):
+    """the drop-in executable with --parity (reference random stream, exact math, CPU texture semantics) writes files that are
+    BYTE-identical to the ones the reference program's own cpu_render + BinarySaver wrote (src/camera.cu:351-394, 128-153;
+    tests/golden/program_frames.npz, 3 frames on the moving camera path) -- both through the executable and through gpu_render"""
+    import os
+    import subprocess
+    (tmp_path / "exe").mkdir()
+    cfg, want = _program_frames_config(tmp_path, "exe")
+    exe = os.path.join(os.path.dirname(rt.LIB_PATH), "rt_main")
+    r = subprocess.run([exe, "--gpu", "--parity"], input=cfg.encode(), capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr.decode()
+    lines = [l.split("\t") for l in r.stdout.decode().strip().split("\n")]
+    assert [l[0] for l in lines] == ["0", "1", "2"] and all(int(l[2]) == 48 * 32 * 4 for l in lines)
+    for i in range(3):
+        got = np.fromfile(tmp_path / "exe" / ("f_%d.bin" % i), np.uint8)
+        assert got.tobytes() == want[i].tobytes(), "frame %d: %d bytes differ" % (i, (got != want[i]).sum())
+    # without --parity: the production stream -- same format, a different (statistically equal) image
+    r = subprocess.run([exe, "--gpu", "--no-pipeline"], input=cfg.encode(), capture_output=True, timeout=300)
+    assert r.returncode == 0
+    prod = np.fromfile(tmp_path / "exe" / "f_1.bin", np.uint8)
+    assert prod[:8].tobytes() == want[1][:8].tobytes() and prod.tobytes() != want[1].tobytes()
+    assert abs(prod[8:].astype(np.float64).mean() - want[1][8:].astype(np.float64).mean()) < 12
+    # the same through the library's gpu_render, several workers, files written in and out of the pipeline
+    for tag, kw in (("lib1", dict(gpus=1)), ("lib3", dict(gpus=3)), ("libnp", dict(gpus=2, pipeline=False))):
+        (tmp_path / tag).mkdir()
+        cfg, _ = _program_frames_config(tmp_path, tag)
+        hs = rt.HostScene(cfg, texture=None)
+        log = hs.gpu_render(0, parity=True, **kw)
+        assert [l.split("\t")[0] for l in log.strip().split("\n")] == ["0", "1", "2"]
+        for i in range(3):
+            assert np.fromfile(tmp_path / tag / ("f_%d.bin" % i), np.uint8).tobytes() == want[i].tobytes()
+
+
+def test_driver_rejects_a_format_string_output_path(rt, tmp_path):
+    hs = rt.HostScene(rt.test_config_text(W=32, H=16, sqrt_spp=1, max_depth=2, output=str(tmp_path / "o_%s_%d.png")), texture="")
+    with pytest.raises(rt.RtError):
+        hs.gpu_render(0)
+    hs = rt.HostScene(rt.test_config_text(W=32, H=16, sqrt_spp=1, max_depth=2, output=str(tmp_path / "o_100%%_%03d.png")), texture="")
+    hs.gpu_render(0)
+    assert (tmp_path / "o_100%_000.png").exists()
+
+
+@pytest.mark.parametrize("n", [2, 8])
+def test_driver_split_tiles_writes_the_single_gpu_files(rt, tmp_path, n):
+    """rt_main --gpus n --split tiles: every frame rendered by n devices together; same bytes on disk as one device"""
+    if rt.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+    outs = {}
+    for tag, kw in (("one", dict(gpus=1)), ("tiles", dict(gpus=n, split_tiles=True))):
+        (tmp_path / tag).mkdir()
+        hs = rt.HostScene(rt.shipped_config_text(W=200, H=120, sqrt_spp=3, max_depth=6, output=str(tmp_path / tag / "f_%d.bin"), num_frames=4), texture="")
+        log = hs.gpu_render(0, **kw)
+        assert [l.split("\t")[0] for l in log.strip().split("\n")] == ["0", "1", "2", "3"]
+        outs[tag] = [np.fromfile(tmp_path / tag / ("f_%d.bin" % i), np.uint8) for i in range(4)]
+    assert all(a.tobytes() == b.tobytes() for a, b in zip(outs["one"], outs["tiles"]))

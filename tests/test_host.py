@@ -22,7 +22,7 @@ def field_equal(a, b, names):
 def test_c_abi_exports_every_declared_symbol(rt):
     hdr = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
     declared = set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", hdr))
-    declared -= {"rt_scene", "rt_render_opts", "rt_work_counters", "rt_scene_stats"}
+    declared -= {"rt_scene", "rt_render_opts", "rt_work_counters", "rt_scene_stats", "rt_trace_opts", "rt_comm", "rt_tiles_info"}
     assert declared == set(rt.C_ABI_SYMBOLS), declared ^ set(rt.C_ABI_SYMBOLS)
     L = C.CDLL(rt.LIB_PATH)
     for name in declared:
@@ -32,6 +32,7 @@ def test_c_abi_exports_every_declared_symbol(rt):
 
 def test_struct_sizes_match_header(rt):
     assert C.sizeof(rt.RenderOpts) == 56 and C.sizeof(rt.WorkCounters) == 48
+    assert C.sizeof(rt.TraceOpts) == 8 and C.sizeof(rt.TilesInfo) == 56 and rt.COMM_ID_BYTES == 128
     assert rt.SPHERE.itemsize == 32 and rt.PLANE.itemsize == 80 and rt.MATERIAL.itemsize == 64 and rt.CAMERA.itemsize == 76
 
 

@@ -28,7 +28,9 @@ def _worker(rank, world, port, W, H, q):
     full = np.stack([xx + 1000 * yy, xx * 0.5, yy * 0.25], -1).astype(np.float32)   # the frame every rank would agree on
     tx, ty = mg.tile_grid(W, H)
     mine = np.zeros_like(full)                                                       # this rank renders only its tiles
-    for t in range(rank, tx * ty, world):
+    for t in range(tx * ty):
+        if rt.tile_owner(t, world)[0] != rank:      # the library's partition (rt_tile_owner, host arithmetic)
+            continue
         x0, y0 = (t % tx) * 16, (t // tx) * 16
         mine[y0:y0 + 16, x0:x0 + 16] = full[y0:y0 + 16, x0:x0 + 16]
     packed = torch.from_numpy(mg.pack_tiles_np(mine, rank, world))
@@ -70,3 +72,24 @@ def test_pack_unpack_numpy_roundtrip():
         fb = rng.random((H, W, 3)).astype(np.float32)
         allp = np.concatenate([mg.pack_tiles_np(fb, r, world) for r in range(world)])
         assert mg.unpack_tiles_np(allp, W, H, world).tobytes() == fb.tobytes()
+
+
+def test_tile_partition_is_a_balanced_bijection():
+    """rt_tile_owner (C) == multi_gpu.tile_owner (numpy mirror); every tile has one owner, every rank gets one tile of every
+    group of `world` consecutive ids, and a rank does not own the same tile columns in every row (the failure of t % world
+    whenever the tiles per row are a multiple of world: 120 at 1080p, 480 at 8K)."""
+    sys.path.insert(0, ROOT)
+    import rtp_b200 as rt
+    from rtp_b200_pkg import multi_gpu as mg
+    for W, H, world in [(1920, 1080, 8), (1920, 1080, 2), (7680, 4320, 8), (200, 100, 3), (16, 16, 4), (64, 48, 1)]:
+        tx, ty = mg.tile_grid(W, H)
+        owners = np.array([rt.tile_owner(t, world) for t in range(tx * ty)])
+        assert [tuple(o) for o in owners] == [mg.tile_owner(t, world) for t in range(tx * ty)]
+        assert all(mg.tile_of_rank(k, r, world) == t for t, (r, k) in enumerate(owners))
+        counts = np.bincount(owners[:, 0], minlength=world)
+        assert counts.max() - counts.min() <= 1
+        for g in range(tx * ty // world):
+            assert sorted(owners[g * world:(g + 1) * world, 0]) == list(range(world))
+        if world > 1 and tx % world == 0 and ty >= 8:
+            cols_row0 = set(np.nonzero(owners[:tx, 0] == 0)[0])
+            assert any(set(np.nonzero(owners[r * tx:(r + 1) * tx, 0] == 0)[0]) != cols_row0 for r in range(1, ty))

@@ -111,6 +111,19 @@ def test_textured_synthetic_frame_vs_fixture(orc, rt):
     assert (ty == g["type_bvh"]).all() and (ix == g["index_bvh"]).all()
 
 
+def test_textured_spheres_frame_vs_fixture(orc):
+    """get_sphere_uv -> tex2D_cpu (include/sphere.h:16-22, include/materials.h:20-51): the fixture's textured material sits on
+    spheres (tests/golden/make_golden_r02.py); the restatement reproduces the reference's frame and the (u, v) of its hits"""
+    g = golden("textured_spheres.npz")
+    sc = orc.scene(g["spheres"], g["planes"], g["materials"], g["tex"], int(g["tex_mat"][0]))
+    fb, segs = sc.render(g["camera"], hit_mode=1, tex_mode=0)
+    assert segs == int(g["segments"][0]) and fb.tobytes() == g["fb_sum"].tobytes()
+    import rtp_b200 as rt
+    ty, ix, rec = sc.trace(rt.pixel_center_rays(g["trace_camera"]), 0)
+    assert (ty == g["type_brute"]).all() and (ix == g["index_brute"]).all()
+    assert (bits(rec) == bits(g["rec_brute"])).all()   # t, normal, u, v, front, material, point
+
+
 def test_oracle_vs_live_reference(orc, ref):
     """where the compiled reference is present: fresh random comparison, bit for bit"""
     rng = np.random.default_rng(7)

@@ -54,7 +54,7 @@ def main():
             tex = rt.synthetic_texture()
             scene = rt.Scene(sp, pl, mt, tex, 0)
             rs = REF.scene(sp, pl, mt, tex, 0) if REF is not None else None
-            for frame in (0, 25):
+            for frame in (0, 25, 50, 75):
                 run("shipped_config_1080x720_2500spp_d50_frame%d" % frame, scene, hs.camera(frame), 2, rs)
         else:
             cfg = rt.CONFIGS[name]
