@@ -54,11 +54,11 @@ typedef struct rt_render_opts {
                                    nranks <= 1 renders everything.  Pixels of other ranks are left untouched. */
     int count_work;             /* 1: also count node visits / leaf tests / shaded hits (slower; for the roofline) */
     int top_nodes_in_smem;      /* -1 default (megakernel: 0, others: 64); 0 off; N>0: stage the first N wide nodes in shared memory */
-    int sample_chunk;           /* megakernel work items split a pixel's samples into chunks that shrink geometrically (2/3 of what
-                                   is left each) down to THIS many samples, at most 6 chunks = 5 scratch planes of W*H*3 floats
-                                   (fewer when device memory is short); chunk sums are added in chunk order, so the frame stays
-                                   deterministic.  0 auto (2 for the Philox stream when spp >= 32); -1 never split a pixel (always
-                                   the case for RT_RNG_REFERENCE: the reference's summation order) */
+    int sample_chunk;           /* megakernel work-item length in samples.  A pixel's chunks are summed in a 64-bit fixed-point
+                                   accumulator (2^-32 units, 24 bytes per pixel of scratch): integer adds commute, so the frame is
+                                   deterministic whatever order the chunks finish in, and equal for every tile partition.
+                                   0 auto (2 for the Philox stream when spp >= 32); -1 never split a pixel (always the case for
+                                   RT_RNG_REFERENCE: the reference's summation order) */
 } rt_render_opts;
 
 typedef struct rt_work_counters {

@@ -82,9 +82,19 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     // sample done: pixel += radiance (src/camera.cu:30), next sample or pixel done
                     acc = add3<X>(acc, ps.L);
                     ++sample;
-                    if (sample >= fp.chunk_start[chunk + 1]) {
-                        float* out = (chunk > 0 ? fp.part + (size_t)(chunk - 1) * W * H * 3 : fp.fb) + 3 * ((size_t)py * W + px);
-                        out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
+                    if (sample >= min(spp, (chunk + 1) * fp.chunk_spp)) {
+                        const size_t pix = 3 * ((size_t)py * W + px);
+                        if (nchunks > 1) {
+                            // fixed point, 2^-32 units: the float -> integer conversion is exact for |v| < 2^31 (below 2^-9 to
+                            // 2^-33 absolute), so the accumulator holds the exact sum of the chunks' fp32 sums in any order
+                            unsigned long long* a = reinterpret_cast<unsigned long long*>(fp.acc) + pix;
+                            atomicAdd(a, (unsigned long long)__float2ll_rn(acc.x * kAccScale));
+                            atomicAdd(a + 1, (unsigned long long)__float2ll_rn(acc.y * kAccScale));
+                            atomicAdd(a + 2, (unsigned long long)__float2ll_rn(acc.z * kAccScale));
+                        } else {
+                            float* out = fp.fb + pix;
+                            out[0] = acc.x; out[1] = acc.y; out[2] = acc.z;
+                        }
                         has_pixel = false;
                     }
                     rt.ref = kRefNeed;
@@ -99,16 +109,16 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     unsigned k = 0;
                     if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
                     k = __shfl_sync(full, k, 0);
-                    // item = (sample chunk, tile, 8x4 block), chunk slowest: the long chunks of every block come first,
-                    // the short ones make up the end of the frame
+                    // item = (tile, 8x4 block, sample chunk); chunk fastest by default: the chunks of a block are in flight
+                    // together, on many SMs, and find the block's part of the tree in L2
                     const unsigned per_chunk = (unsigned)fp.my_tiles * kBlocksPerTile;
                     if (k >= per_chunk * (unsigned)nchunks) { exhausted = true; break; }
-                    const unsigned kb = k % per_chunk;
+                    const unsigned kb = fp.chunk_major ? k % per_chunk : k / (unsigned)nchunks;
                     const int tile = tile_of_rank((int)(kb / kBlocksPerTile), fp.tile_rank, fp.tile_nranks);  // >= tile count: no pixels
                     const int blk = (int)(kb % kBlocksPerTile);  // 8 blocks of 8x4 pixels inside the 16x16 tile
                     pool_x0 = (tile % fp.tiles_x) * kTile + (blk & 1) * 8;
                     pool_y0 = (tile / fp.tiles_x) * kTile + (blk >> 1) * 4;
-                    pool_chunk = (int)(k / per_chunk);
+                    pool_chunk = (int)(fp.chunk_major ? k / per_chunk : k % (unsigned)nchunks);
                     pool_next = 0;
                 }
                 int avail = kBlockPixels - pool_next;
@@ -124,7 +134,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                         has_pixel = true;
                         px = x; py = y;
                         chunk = pool_chunk;
-                        sample = fp.chunk_start[pool_chunk];
+                        sample = pool_chunk * fp.chunk_spp;
                         acc = mk3(0, 0, 0);
                         pixel_base = pixel_seed_base(x, y, W);
                     }
@@ -231,7 +241,7 @@ cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rn
 // ---------------------------------------------------------------- primary-ray closest hit (parity entry point)
 // X = true: the exact-math leaf tests (the reference's operation order, include/sphere.h:24-47, include/plane.h:57-96).
 // X = false: the PRODUCTION arithmetic -- the very functions render_mega<.., false, ..> is built from (trav_begin with the
-// hoisted primitives, trav_leaf_pop -> sphere_t<false> / plane_fast_t, trav_inner<false> with the un-widened slab test, the
+// hoisted primitives, trav_leaf_pop -> sphere_t<false> / plane_t<false>, trav_inner<false> with the un-widened slab test, the
 // SFU approximations as compiled for the device), driven by the megakernel's own loop shape, so the ids / t this entry
 // point returns are the ids / t the benchmarked kernel shades.
 template <bool X>
@@ -291,52 +301,29 @@ cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n
                  : launch_trace_primary_t<false>(sc, d_rays6, n, tmin, tmax, d_type, d_index, d_t, num_sms, stream);
 }
 
-// ---------------------------------------------------------------- sum of the sample chunks (render_mega with nchunks > 1)
-// fb holds chunk 0's sums, part[c-1] chunk c's: fb = ((fb + part[0]) + part[1]) + ... for the pixels of this rank's tiles
-// (the other pixels of the planes were never written).  A tile row is 48 consecutive floats; when rows are 16-byte aligned
-// (W % 4 == 0) a thread handles one float4 of them, 12 per row, 192 per tile.
-template <bool VEC>
-__global__ void reduce_chunks_kernel(const __grid_constant__ FrameParams fp) {
+// ---------------------------------------------------------------- sample chunks -> framebuffer (render_mega with nchunks > 1)
+// fb = float(acc) * 2^-32 for the pixels of this rank's tiles (the other pixels of fb are not this rank's to write).
+// A tile row is 48 consecutive values: one thread per value, 3 x 16 threads per row.
+__global__ void finalize_chunks_kernel(const __grid_constant__ FrameParams fp) {
     const int W = fp.cam.W, H = fp.cam.H;
-    const size_t plane = (size_t)W * H * 3;
     const int ntiles = fp.tiles_x * fp.tiles_y;
     for (int k = blockIdx.x; k < fp.my_tiles; k += gridDim.x) {
         const int t = tile_of_rank(k, fp.tile_rank, fp.tile_nranks);
         if (t >= ntiles) continue;
         const int x0 = (t % fp.tiles_x) * kTile, y0 = (t / fp.tiles_x) * kTile;
-        if (VEC) {
-            const int row = threadIdx.x / 12, q = threadIdx.x % 12;  // 16 rows x 12 float4
-            const int y = y0 + row, x = x0 + (q * 4) / 3;            // first pixel the float4 touches
-            if (row < kTile && y < H && x < W) {                     // W % 4 == 0 and x0 % 16 == 0: a float4 never straddles the row end
-                const size_t i = 3 * ((size_t)y * W + x0) + 4 * (size_t)q;
-                float4 a = *reinterpret_cast<const float4*>(fp.fb + i);
-                for (int c = 0; c + 1 < fp.nchunks; ++c) {
-                    const float4 b = __ldcs(reinterpret_cast<const float4*>(fp.part + c * plane + i));
-                    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-                }
-                *reinterpret_cast<float4*>(fp.fb + i) = a;
-            }
-        } else {
-            for (int p = threadIdx.x; p < kTile * kTile; p += blockDim.x) {
-                const int x = x0 + (p & 15), y = y0 + (p >> 4);
-                if (x < W && y < H) {
-                    const size_t i = 3 * ((size_t)y * W + x);
-                    float r = fp.fb[i], g = fp.fb[i + 1], b = fp.fb[i + 2];
-                    for (int c = 0; c + 1 < fp.nchunks; ++c) {
-                        const float* q = fp.part + c * plane + i;
-                        r += q[0]; g += q[1]; b += q[2];
-                    }
-                    fp.fb[i] = r; fp.fb[i + 1] = g; fp.fb[i + 2] = b;
-                }
+        const int nx = min(kTile, W - x0) * 3;  // values per row of this tile
+        for (int q = threadIdx.x; q < kTile * kTile * 3; q += blockDim.x) {
+            const int row = q / (kTile * 3), c = q % (kTile * 3);
+            const int y = y0 + row;
+            if (y < H && c < nx) {
+                const size_t i = 3 * ((size_t)y * W + x0) + c;
+                fp.fb[i] = __ll2float_rn(__ldcs(fp.acc + i)) * kAccInvScale;
             }
         }
     }
 }
-cudaError_t launch_reduce_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream) {
-    // vector path: rows of the frame AND of every plane 16-byte aligned (cudaMalloc bases are; W % 4 == 0 keeps the rows)
-    const bool vec = fp.cam.W % 4 == 0 && ((uintptr_t)fp.fb & 15) == 0 && ((uintptr_t)fp.part & 15) == 0;
-    if (vec) reduce_chunks_kernel<true><<<num_sms * 8, 192, 0, stream>>>(fp);
-    else reduce_chunks_kernel<false><<<num_sms * 8, 256, 0, stream>>>(fp);
+cudaError_t launch_finalize_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream) {
+    finalize_chunks_kernel<<<num_sms * 8, 256, 0, stream>>>(fp);
     return cudaGetLastError();
 }
 

@@ -7,8 +7,6 @@
 
 namespace rtb {
 
-constexpr int kMaxChunks = 8;
-
 struct FrameParams {
     CameraPod cam;
     uint2 key;          // Philox key
@@ -18,13 +16,13 @@ struct FrameParams {
     int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
     int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
     float* fb;                        // W*H*3 sums
-    // sample chunks (render_mega only): a work item is (8x4 pixel block, samples [chunk_start[c], chunk_start[c+1])).  Chunk 0
-    // accumulates into fb itself, chunk c > 0 into part[c-1][pixel], and reduce_chunks adds the planes to fb in chunk order.
-    // Chunks shrink geometrically (the long ones are queued first, the short ones form the end of the frame), so a handful of
-    // planes gives the frame a tail of a few samples per lane.
-    float* part;
-    int nchunks;
-    int chunk_start[kMaxChunks + 1];
+    // sample chunks (render_mega only): a work item is (8x4 pixel block, chunk of chunk_spp samples).  With nchunks > 1 a lane
+    // adds its chunk's partial sum to the pixel's 64-bit FIXED-POINT accumulator acc[pixel][channel] (value * 2^32, one
+    // RED.ADD.U64 per channel and item); integer addition is associative, so the frame does not depend on the order in
+    // which the chunks arrive, and finalize_chunks converts the sums to float once.  nchunks == 1: the lane stores to fb.
+    long long* acc;
+    int chunk_spp, nchunks;
+    int chunk_major;                  // item order: 0 = (block, chunk) chunk fastest; 1 = all blocks of chunk 0, then chunk 1, ...
     unsigned int* tile_counter;       // work queue head (zeroed before launch)
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
 };
@@ -86,8 +84,9 @@ cudaError_t launch_render_wavefront(const DevScene& sc, const FrameParams& fp, i
 // exact = 1: the reference's leaf arithmetic; 0: the production (fast fp32 + SFU) arithmetic of render_mega
 cudaError_t launch_trace_primary(const DevScene& sc, const float* d_rays6, int n, float tmin, float tmax, int exact, int* d_type,
                                  int* d_index, float* d_t, int num_sms, cudaStream_t stream);
-// fb[pixel] += part[0][pixel] + part[1][pixel] + ... (in chunk order: deterministic) for the pixels of this rank's tiles
-cudaError_t launch_reduce_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream);
+// fb[pixel] = float(acc[pixel]) * 2^-32 for the pixels of this rank's tiles (render_mega with nchunks > 1)
+cudaError_t launch_finalize_chunks(const FrameParams& fp, int num_sms, cudaStream_t stream);
+constexpr float kAccScale = 4294967296.0f, kAccInvScale = 2.3283064365386963e-10f;  // 2^32, 2^-32
 cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, int num_sms, cudaStream_t stream);
 cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, int num_sms, cudaStream_t stream);
 // skip_rank >= 0: leave that rank's tiles alone (they are already in d_fb: the caller rendered them there)

@@ -281,7 +281,7 @@ void rt_scene_destroy(rt_scene* s) {
     if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
     if (s->tex_array) cudaFreeArray(s->tex_array);
     void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
-                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_part, s->d_packed};
+                    s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_acc, s->d_packed};
     for (void* b : bufs)
         if (b) cudaFree(b);
     if (s->ev0) cudaEventDestroy(s->ev0);
@@ -336,31 +336,6 @@ int ensure_framebuffer(rt_scene* s, size_t n) {
     return RT_OK;
 }
 
-// Sample chunks of the megakernel (kernels.h, FrameParams): sizes shrink geometrically -- each chunk takes `keep` of what is
-// left -- down to `last` samples, at most kMaxChunks of them.  chunk 0 accumulates in the framebuffer; every further chunk
-// needs one scratch plane of W*H*3 floats.  Returns the number of chunks and fills start[0..n].
-static int plan_chunks(int spp, int last, int max_chunks, int* start) {
-    double keep = 2.0 / 3.0;
-    if (const char* e = getenv("RTB_CHUNK_KEEP")) keep = atof(e);
-    if (!(keep >= 0.25 && keep <= 0.9)) keep = 2.0 / 3.0;
-    if (last < 1) last = 1;
-    int n = 0, done = 0;
-    start[0] = 0;
-    while (done < spp) {
-        int left = spp - done, take;
-        if (n + 1 >= max_chunks || left <= last) take = left;
-        else {
-            take = (int)(left * keep + 0.5);
-            if (take < last) take = last;
-            if (left - take < last) take = left - last;  // never leave a remainder shorter than the last chunk
-            if (take < 1) take = left;
-        }
-        done += take;
-        start[++n] = done;
-    }
-    return n;
-}
-
 int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, float* d_fb, cudaStream_t stream) {
     if (!s || !cam76 || !d_fb) return fail(RT_ERR_INVALID, "rt_render: NULL argument");
     rt_render_opts o = resolve_opts(opts_in);
@@ -381,43 +356,36 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     fp.fb = d_fb;
     fp.tile_counter = s->d_tile_counter;
     fp.counters = s->d_counters;
-    // sample chunks: shorter work items at the end of the frame (the tail is what limits strong scaling over GPUs).
-    // Only the production stream is chunked: parity mode keeps the reference's per-pixel summation order bit for bit.
-    fp.part = nullptr;
+    // sample chunks: work items of a few samples (the tail is what limits strong scaling over GPUs, and short items keep a
+    // warp's lanes on the same few pixels and in step: measured, items of 171 samples render the headline frame 6 % slower
+    // than items of 2).  Only the production stream is chunked: parity mode keeps the reference's per-pixel summation order.
+    fp.acc = nullptr;
+    fp.chunk_spp = fp.cam.spp > 0 ? fp.cam.spp : 1;
     fp.nchunks = 1;
-    fp.chunk_start[0] = 0;
-    fp.chunk_start[1] = fp.cam.spp;
-    int want_chunk = o.sample_chunk;   // > 0: length of the LAST chunk(s); 0: auto; < 0: never split
+    fp.chunk_major = 0;
+    if (const char* e = getenv("RTB_CHUNK_MAJOR")) fp.chunk_major = atoi(e) ? 1 : 0;
+    int want_chunk = o.sample_chunk;
     if (o.rng != RT_RNG_PHILOX) want_chunk = -1;
-    if (want_chunk == 0) want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 2 : -1;
+    if (want_chunk == 0) {
+        want_chunk = (o.rng == RT_RNG_PHILOX && o.kernel == RT_KERNEL_MEGA && fp.cam.spp >= 32) ? 2 : -1;
+        if (const char* e = getenv("RTB_SAMPLE_CHUNK")) want_chunk = atoi(e) > 0 ? atoi(e) : -1;
+    }
     if (want_chunk > 0 && o.kernel == RT_KERNEL_MEGA && fp.cam.spp > want_chunk && fp.cam.depth > 0) {
-        // scratch: one plane per chunk after the first, at most a quarter of the free device memory and never more than 1 GiB
-        // (6 planes of a 1080p frame are 149 MB; an 8K frame gets 2); if the allocation fails the frame renders with fewer
-        // chunks, in the end unsplit -- a longer tail, the same samples
-        const size_t plane_bytes = (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(float);
-        int max_chunks = 6;
-        if (const char* e = getenv("RTB_MAX_CHUNKS")) max_chunks = atoi(e);
-        if (max_chunks > kMaxChunks) max_chunks = kMaxChunks;
-        if (max_chunks < 1) max_chunks = 1;
-        size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); free_b = 0; }
-        size_t budget = (free_b + s->part_floats * sizeof(float)) / 4;
-        if (budget > ((size_t)1 << 30)) budget = (size_t)1 << 30;
-        while (max_chunks > 1 && (size_t)(max_chunks - 1) * plane_bytes > budget) --max_chunks;
-        for (;;) {
-            fp.nchunks = plan_chunks(fp.cam.spp, want_chunk, max_chunks, fp.chunk_start);
-            if (fp.nchunks <= 1) break;
-            const size_t need = (size_t)(fp.nchunks - 1) * fp.cam.W * fp.cam.H * 3;
-            if (s->part_floats >= need) break;
-            if (s->d_part) cudaFree(s->d_part);
-            s->d_part = nullptr;
-            s->part_floats = 0;
-            if (cudaMalloc((void**)&s->d_part, need * sizeof(float)) == cudaSuccess) { s->part_floats = need; break; }
-            cudaGetLastError();
-            max_chunks = fp.nchunks - 1;  // out of memory: try with one plane less
+        // the chunks of a pixel meet in a 64-bit fixed-point accumulator plane (2 x the framebuffer's bytes, L2 resident at
+        // 1080p); if it cannot be allocated the frame renders unsplit -- a longer tail, the same samples
+        const size_t need = (size_t)fp.cam.W * fp.cam.H * 3;
+        if (s->acc_values < need) {
+            if (s->d_acc) cudaFree(s->d_acc);
+            s->d_acc = nullptr;
+            s->acc_values = 0;
+            if (cudaMalloc((void**)&s->d_acc, need * sizeof(long long)) == cudaSuccess) s->acc_values = need;
+            else cudaGetLastError();
         }
-        if (fp.nchunks > 1) fp.part = s->d_part;
-        else { fp.nchunks = 1; fp.chunk_start[0] = 0; fp.chunk_start[1] = fp.cam.spp; }
+        if (s->d_acc) {
+            fp.chunk_spp = want_chunk;
+            fp.nchunks = (fp.cam.spp + want_chunk - 1) / want_chunk;
+            fp.acc = s->d_acc;
+        }
     }
     DevScene dev = s->dev;
     // megakernel default: no staging (measured no gain); the other kernels keep the 64-node default
@@ -438,10 +406,11 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, 64, stream));
     RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
     RT_CUDA(cudaEventRecord(s->ev0, stream));
+    if (fp.acc) RT_CUDA(cudaMemsetAsync(fp.acc, 0, (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(long long), stream));  // inside the timed region
     if (o.kernel == RT_KERNEL_MEGA) RT_CUDA(launch_render_mega(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else if (o.kernel == RT_KERNEL_POOL) RT_CUDA(launch_render_pool(dev, fp, o.rng, o.exact_math, o.count_work, cfg, stream));
     else RT_CUDA(launch_render_wavefront(dev, fp, o.rng, o.exact_math, o.count_work, cfg, s->wf, stream));
-    if (fp.nchunks > 1) RT_CUDA(launch_reduce_chunks(fp, s->num_sms, stream));
+    if (fp.nchunks > 1) RT_CUDA(launch_finalize_chunks(fp, s->num_sms, stream));
     RT_CUDA(cudaEventRecord(s->ev1, stream));
     s->pending = true;
     s->pending_stream = stream;

@@ -79,8 +79,8 @@ struct rt_scene {
     void* d_trace = nullptr;
     size_t trace_bytes = 0;
     rtb::WavefrontScratch wf;
-    float* d_part = nullptr;   // partial sums of the sample chunks 1.. (render_mega); chunk 0 accumulates in the framebuffer
-    size_t part_floats = 0;
+    long long* d_acc = nullptr;  // fixed-point accumulators of the sample chunks (render_mega), W*H*3 values
+    size_t acc_values = 0;
     float* d_packed = nullptr; // rt_render_tiles: nranks packed tile buffers on rank 0 (own slot unused), one elsewhere
     size_t packed_floats = 0;
     cudaEvent_t ev2 = nullptr; // end of the gather + unpack of rt_render_tiles

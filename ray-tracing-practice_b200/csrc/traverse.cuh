@@ -44,8 +44,10 @@ struct DevScene {
 #ifndef RTB_FAST_RCP
 #define RTB_FAST_RCP 1
 #endif
+// RTB_FAST_PLANE=1 selects the two-dot-product plane record (plane_fast_t) in fast mode.  It was the production default of
+// round 1 (1-2 % faster) and is OFF now: it decides edge hits differently from the reference (see plane_t).
 #ifndef RTB_FAST_PLANE
-#define RTB_FAST_PLANE 1
+#define RTB_FAST_PLANE 0
 #endif
 #ifndef RTB_FAST_SLAB
 #define RTB_FAST_SLAB 1
@@ -88,12 +90,24 @@ __device__ __forceinline__ float leaf_sqrt(float D) {
 }
 
 // include/sphere.h:24-47.  a = |d|^2 and (fast mode) 1/a are per-ray constants.
+//
+// BOTH policies form the discriminant exactly as the reference does -- oc, hb, c and D = hb*hb - a*c as separately rounded
+// fp32 operations in its order.  D is the difference of two numbers of size |oc|^2 |d|^2 that agree to all but the last
+// few bits (r << |oc|): its value, and for a grazing ray its SIGN, is decided by how the products round.  An FMA-contracted
+// evaluation is no less accurate, but it is a different answer: measured on the 10k-sphere 1080p frame it moved t by up
+// to 1.8e-4 relative and changed the hit primitive of 2e-4 of the primary rays against the reference (north_star's gates
+// are 1e-5 and "ids equal").  What the fast policy keeps is everything after D: the 2-ulp SFU square root and the
+// reciprocal multiply instead of the IEEE square root and the double-precision division (relative effect on t: ~3e-7).
 template <bool X>
 __device__ __forceinline__ bool sphere_t(V3 o, V3 d, float a, float inv_a, float4 s, float tmin, float tmax, float& t_out) {
-    V3 oc = sub3<X>(o, mk3(s.x, s.y, s.z));
-    float hb = dot3<X>(oc, d);
-    float cc = fsub<X>(len2_3<X>(oc), fmul<X>(s.w, s.w));
-    float D = fsub<X>(fmul<X>(hb, hb), fmul<X>(a, cc));
+#ifndef RTB_FAST_SPHERE_D
+#define RTB_FAST_SPHERE_D 0
+#endif
+    constexpr bool XD = X || !RTB_FAST_SPHERE_D;  // arithmetic policy of the discriminant
+    V3 oc = sub3<XD>(o, mk3(s.x, s.y, s.z));
+    float hb = dot3<XD>(oc, d);
+    float cc = fsub<XD>(len2_3<XD>(oc), fmul<XD>(s.w, s.w));
+    float D = fsub<XD>(fmul<XD>(hb, hb), fmul<XD>(a, cc));
     if (D < 0.0f) return false;
     float sq = leaf_sqrt<X>(D);
     float t;
@@ -115,36 +129,51 @@ __device__ __forceinline__ bool sphere_t(V3 o, V3 d, float a, float inv_a, float
 }
 
 // include/plane.h:57-96 incl. the interior tests :30-55.  p -> the plane's 5 float4.
+//
+// As for the sphere, BOTH policies evaluate t's operands, the hit point and the interior coordinates alpha, beta in the
+// reference's operation order without contraction: a ray through the shared edge of two faces of a solid has alpha or beta
+// within rounding of 0 (the BASELINE camera looks along such an edge: a whole column of pixel centres has |beta| ~ 3e-8),
+// and whether it is accepted, by which face, or falls through the crack is decided by the last bit.  The fast policy
+// replaces only the reference's double-precision operations by fp32 ones that round to the same value: the division
+// (IEEE fp32 division == the double quotient rounded to float, except on exact double-rounding ties) and the triangle's
+// alpha + beta > 1 (fp32 sum, with the exact rounding error consulted when the sum rounds to 1).
 template <bool X>
 __device__ __forceinline__ bool plane_t(V3 o, V3 d, const float4* __restrict__ p, float tmin, float tmax, float& t_out,
                                         float& alpha_out, float& beta_out) {
     float4 nD = __ldg(p);
     V3 n = mk3(nD.x, nD.y, nD.z);
-    float denom = dot3<X>(n, d);
-    if (fabsf(denom) < 1e-8f) {
-        // reference compares float |denom| with the DOUBLE literal 1e-8: equal to the fp32 compare unless
-        // |denom| lies between 1e-8 and fp32(1e-8)
-        if (!X || (double)fabsf(denom) < 1e-8) return false;
-    }
-    float num = fsub<X>(nD.w, dot3<X>(n, o));
-    float t = X ? (float)((double)num / (double)denom) : __fdividef(num, denom);
+    float denom = dot3<true>(n, d);
+    // the reference compares float |denom| with the DOUBLE literal 1e-8 (include/plane.h:59): true exactly for
+    // |denom| <= fp32(1e-8) = 9.99999994e-9
+    if (fabsf(denom) <= 1e-8f) return false;
+    float num = __fsub_rn(nD.w, dot3<true>(n, o));
+    float t = X ? (float)((double)num / (double)denom) : __fdiv_rn(num, denom);
     if (!(tmin <= t && t <= tmax)) return false;
     float4 wT = __ldg(p + 1), u4 = __ldg(p + 2), v4 = __ldg(p + 3), b4 = __ldg(p + 4);
-    V3 ip = add3<X>(o, scale3<X>(t, d));
-    V3 ph = sub3<X>(ip, mk3(b4.x, b4.y, b4.z));
+    V3 ip = add3<true>(o, scale3<true>(t, d));
+    V3 ph = sub3<true>(ip, mk3(b4.x, b4.y, b4.z));
     V3 w = mk3(wT.x, wT.y, wT.z);
-    float alpha = dot3<X>(w, cross3<X>(ph, mk3(v4.x, v4.y, v4.z)));
-    float beta = dot3<X>(w, cross3<X>(mk3(u4.x, u4.y, u4.z), ph));
+    float alpha = dot3<true>(w, cross3<true>(ph, mk3(v4.x, v4.y, v4.z)));
+    float beta = dot3<true>(w, cross3<true>(mk3(u4.x, u4.y, u4.z), ph));
     int type = __float_as_int(wT.w);
     if (type == 0) {  // QUAD
         if (!(0.0f <= alpha && alpha <= 1.0f) || !(0.0f <= beta && beta <= 1.0f)) return false;
-    } else if (type == 1) {  // ELLIPSE: powf(a-.5,2)+powf(b-.5,2) > .25 rejects
-        float da = X ? (float)((double)alpha - 0.5) : alpha - 0.5f;
-        float db = X ? (float)((double)beta - 0.5) : beta - 0.5f;
-        if (fadd<X>(fmul<X>(da, da), fmul<X>(db, db)) > 0.25f) return false;
-    } else if (type == 2) {  // TRIANGLE: the reference forms alpha+beta in double
+    } else if (type == 1) {  // ELLIPSE: powf(a-.5,2)+powf(b-.5,2) > .25 rejects; (double)alpha - 0.5 is exact, so its float is the fp32 difference
+        float da = __fsub_rn(alpha, 0.5f), db = __fsub_rn(beta, 0.5f);
+        if (__fadd_rn(__fmul_rn(da, da), __fmul_rn(db, db)) > 0.25f) return false;
+    } else if (type == 2) {  // TRIANGLE: the reference forms alpha+beta in double (exact) and compares with 1.0
         if (alpha < 0.0f || beta < 0.0f) return false;
-        if (X ? ((double)alpha + (double)beta > 1.0) : (alpha + beta > 1.0f)) return false;
+        if (X) {
+            if ((double)alpha + (double)beta > 1.0) return false;
+        } else {
+            const float sum = __fadd_rn(alpha, beta);
+            if (sum > 1.0f) return false;
+            if (sum == 1.0f) {  // the exact sum is 1 + err: TwoSum's error term (Knuth), exact in fp32
+                const float bv = __fsub_rn(sum, alpha);
+                const float err = __fadd_rn(__fsub_rn(alpha, __fsub_rn(sum, bv)), __fsub_rn(beta, bv));
+                if (err > 0.0f) return false;
+            }
+        }
     }
     t_out = t;
     alpha_out = alpha;
@@ -236,7 +265,7 @@ __device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, fl
 #endif
     { r.idx = 1.0f / dx; r.idy = 1.0f / dy; r.idz = 1.0f / dz; }
     r.oox = o.x * r.idx; r.ooy = o.y * r.idy; r.ooz = o.z * r.idz;
-    r.a = len2_3<X>(d);
+    r.a = len2_3<true>(d);  // exactly the reference's a = |d|^2 (include/sphere.h:27): it multiplies into the discriminant
 #if RTB_FAST_RCP && defined(__CUDA_ARCH__)
     r.inv_a = X ? 0.0f : __fdividef(1.0f, r.a);
 #else
@@ -389,10 +418,21 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
                     r.horig = orig;
                 }
             } else {
-                // production: exact ties have measure zero; no caller's index, no key (two registers and a load less)
-                r.closest = t;
-                r.htype = type;
-                r.hslot = first + k;
+                // production: no caller's index and no key are carried (two registers and a load less).  An exact tie
+                // t == closest has measure zero for generic rays, but the shared edge of two faces of a solid produces it
+                // (both faces accept the edge point at the same t); only then are the two callers' indices fetched, and the
+                // reference's rule applied: the later primitive in (spheres, then planes) array order wins.
+                bool take = true;
+                if (t == r.closest && r.htype >= 0) {
+                    const int orig = type == 0 ? __ldg(sc.sphere_meta + first + k).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)(first + k) + 3).w);
+                    const int best = r.htype == 0 ? __ldg(sc.sphere_meta + r.hslot).y : __float_as_int(__ldg(sc.planes + 5 * (size_t)r.hslot + 3).w);
+                    take = (((unsigned int)type << 30) | (unsigned int)orig) > (((unsigned int)r.htype << 30) | (unsigned int)best);
+                }
+                if (take) {
+                    r.closest = t;
+                    r.htype = type;
+                    r.hslot = first + k;
+                }
             }
         }
     }
