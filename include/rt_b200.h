@@ -165,7 +165,9 @@ unsigned long long rt_tiles_packed_floats(int width, int height, int nranks); /*
  * One rank per GPU -- a process (torchrun, MPI) or a thread of one process.  Every rank holds the whole scene (its own
  * rt_scene on its own device) and calls rt_render_tiles with the same camera and options: each renders its interleaved
  * tiles, the packed tiles go to rank 0 with grouped ncclSend / ncclRecv over NVLink, rank 0 assembles the frame on its
- * device and downloads it once.  NCCL is bound at run time (dlopen); without it nranks > 1 fails with RT_ERR_UNSUPPORTED. */
+ * device and downloads it once.  NCCL is bound at run time: the libnccl.so.2 the process already holds (e.g. the one torch
+ * loaded), else $RTB_NCCL_LIB, else the system library; without one nranks > 1 fails with RT_ERR_UNSUPPORTED.  A process that
+ * also uses torch should import it BEFORE the first rt_comm_* call, so that both share one NCCL. */
 typedef struct rt_comm rt_comm;
 #define RT_COMM_ID_BYTES 128
 /* rank 0: an ncclUniqueId (RT_COMM_ID_BYTES bytes) to hand to every rank by the launcher's own means (MPI_Bcast, a

@@ -386,9 +386,10 @@ cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nra
     tiles_pack_kernel<<<num_sms * 4, kTile * kTile, 0, stream>>>(d_fb, W, H, rank, nranks, d_packed);
     return cudaGetLastError();
 }
-cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, float* d_fb, int num_sms,
-                                cudaStream_t stream) {
-    tiles_unpack_kernel<<<num_sms * 4, kTile * kTile, 0, stream>>>(d_packed_all, W, H, nranks, skip_rank, tiles_packed_floats(W, H, nranks), d_fb);
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, size_t rank_stride, float* d_fb,
+                                int num_sms, cudaStream_t stream) {
+    if (rank_stride == 0) rank_stride = tiles_packed_floats(W, H, nranks);
+    tiles_unpack_kernel<<<num_sms * 4, kTile * kTile, 0, stream>>>(d_packed_all, W, H, nranks, skip_rank, rank_stride, d_fb);
     return cudaGetLastError();
 }
 

@@ -89,9 +89,10 @@ cudaError_t launch_finalize_chunks(const FrameParams& fp, int num_sms, cudaStrea
 constexpr float kAccScale = 4294967296.0f, kAccInvScale = 2.3283064365386963e-10f;  // 2^32, 2^-32
 cudaError_t launch_tonemap(const float* d_fb, size_t n_values, int divisor, unsigned char* d_out, int num_sms, cudaStream_t stream);
 cudaError_t launch_tiles_pack(const float* d_fb, int W, int H, int rank, int nranks, float* d_packed, int num_sms, cudaStream_t stream);
-// skip_rank >= 0: leave that rank's tiles alone (they are already in d_fb: the caller rendered them there)
-cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, float* d_fb, int num_sms,
-                                cudaStream_t stream);
+// skip_rank >= 0: leave that rank's tiles alone (they are already in d_fb: the caller rendered them there); rank_stride:
+// floats between two ranks' packed buffers (0 = tiles_packed_floats, i.e. back to back)
+cudaError_t launch_tiles_unpack(const float* d_packed_all, int W, int H, int nranks, int skip_rank, size_t rank_stride, float* d_fb,
+                                int num_sms, cudaStream_t stream);
 size_t tiles_packed_floats(int W, int H, int nranks);
 size_t mega_smem_bytes(int top_nodes, int threads);
 

@@ -382,6 +382,11 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
             else cudaGetLastError();
         }
         if (s->d_acc) {
+            // at most kMaxChunksPerPixel items per pixel: beyond that the accumulator's atomics cost more than the shorter items
+            // gain (measured on the shipped scene at 2500 spp: 1250 chunks of 2 render 7 % slower than 125 of 20)
+            const int kMaxChunksPerPixel = 128;
+            if (o.sample_chunk <= 0 && (fp.cam.spp + want_chunk - 1) / want_chunk > kMaxChunksPerPixel)
+                want_chunk = (fp.cam.spp + kMaxChunksPerPixel - 1) / kMaxChunksPerPixel;
             fp.chunk_spp = want_chunk;
             fp.nchunks = (fp.cam.spp + want_chunk - 1) / want_chunk;
             fp.acc = s->d_acc;
@@ -549,7 +554,7 @@ int rt_tiles_pack(rt_scene* s, const void* d_fb, int W, int H, int rank, int nra
 int rt_tiles_unpack(rt_scene* s, const void* d_all, int W, int H, int nranks, void* d_fb, void* stream) {
     if (!s || !d_fb || !d_all || nranks < 1) return fail(RT_ERR_INVALID, "rt_tiles_unpack: bad argument");
     DeviceGuard guard(s->device);
-    RT_CUDA(launch_tiles_unpack((const float*)d_all, W, H, nranks, -1, (float*)d_fb, s->num_sms, (cudaStream_t)stream));
+    RT_CUDA(launch_tiles_unpack((const float*)d_all, W, H, nranks, -1, 0, (float*)d_fb, s->num_sms, (cudaStream_t)stream));
     return RT_OK;
 }
 void rt_tile_owner(int tile, int nranks, int* rank, int* k) {

@@ -47,12 +47,15 @@ NcclApi& nccl() {
     static NcclApi api;
     static std::once_flag once;
     std::call_once(once, [] {
+        // a copy the process already holds (torch's bundled one, when torch was imported first) is the one to share; else
+        // RTB_NCCL_LIB, else the system library.  Loaded RTLD_LOCAL: nothing else should resolve against our choice.
         const char* names[] = {getenv("RTB_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        api.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
         for (const char* n : names) {
-            if (!n || !*n) continue;
-            api.lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
             if (api.lib) break;
-            api.why = dlerror();
+            if (!n || !*n) continue;
+            api.lib = dlopen(n, RTLD_NOW | RTLD_LOCAL);
+            if (!api.lib) api.why = dlerror();
         }
         if (!api.lib) return;
         auto sym = [&](const char* n) {
@@ -214,7 +217,7 @@ int rt_render_tiles(rt_scene* s, rt_comm* c, const void* cam76, const rt_render_
             RT_NCCL(nccl().GroupStart());
             for (int r = 1; r < nranks; ++r) RT_NCCL(nccl().Recv(s->d_packed + (size_t)r * stride, stride, kNcclFloat, r, c->comm, st));
             RT_NCCL(nccl().GroupEnd());
-            RT_CUDA(launch_tiles_unpack(s->d_packed, cam.W, cam.H, nranks, 0, s->d_fb, s->num_sms, st));  // rank 0's tiles are in place
+            RT_CUDA(launch_tiles_unpack(s->d_packed, cam.W, cam.H, nranks, 0, stride, s->d_fb, s->num_sms, st));  // rank 0's tiles are in place
             gathered = (unsigned long long)(nranks - 1) * stride * sizeof(float);
         } else {
             RT_NCCL(nccl().Send(mine, stride, kNcclFloat, 0, c->comm, st));

@@ -44,10 +44,10 @@ struct DevScene {
 #ifndef RTB_FAST_RCP
 #define RTB_FAST_RCP 1
 #endif
-// RTB_FAST_PLANE=1 selects the two-dot-product plane record (plane_fast_t) in fast mode.  It was the production default of
-// round 1 (1-2 % faster) and is OFF now: it decides edge hits differently from the reference (see plane_t).
+// RTB_FAST_PLANE=1: fast mode tests planes on the two-dot-product record (plane_fast_t) and hands only the hits near the
+// polygon's outline to the reference-order test; 0: always the reference-order test (plane_t).
 #ifndef RTB_FAST_PLANE
-#define RTB_FAST_PLANE 0
+#define RTB_FAST_PLANE 1
 #endif
 #ifndef RTB_FAST_SLAB
 #define RTB_FAST_SLAB 1
@@ -181,30 +181,47 @@ __device__ __forceinline__ bool plane_t(V3 o, V3 d, const float4* __restrict__ p
     return true;
 }
 
-// Fast-mode plane test on the 3 x float4 record of lbvh.cuh (plane_fast_record): t from (n, D); the interior coordinates as
-// alpha = A.o + t A.d - a0, beta likewise -- 48 bytes and ~30 instructions instead of 80 bytes and ~55.
-__device__ __forceinline__ bool plane_fast_t(V3 o, V3 d, const float4* __restrict__ q, float tmin, float tmax, float& t_out) {
+// Fast-mode plane test: the 3 x float4 record of lbvh.cuh (plane_fast_record) first -- t from (n, D), the interior
+// coordinates as alpha = A.o + t A.d - a0, beta likewise: 48 bytes and ~30 instructions instead of 80 bytes and ~65 -- and the
+// reference-order test (plane_t) only for the hits it cannot decide: those within kEdgeEps of the polygon's outline, where the
+// two evaluations of alpha / beta (they agree to a few 1e-6) could fall on different sides.  Everywhere else the decision is
+// the reference's, and t differs from the reference's by fp32 rounding (~3e-7 relative: no cancellation in t's operands).
+constexpr float kEdgeEps = 1e-4f, kTieEps = 1e-6f;
+__device__ __forceinline__ bool plane_fast_t(V3 o, V3 d, const float4* __restrict__ q, const float4* __restrict__ p, float tmin,
+                                             float tmax, float& t_out) {
     const float4 nD = __ldg(q);
     const float denom = fmaf(nD.z, d.z, fmaf(nD.y, d.y, nD.x * d.x));
-    if (fabsf(denom) < 1e-8f) return false;
+    if (fabsf(denom) < 2e-8f) {  // (almost) parallel: the reference's own |denom| < 1e-8 rule decides
+        float al, be;
+        return plane_t<false>(o, d, p, tmin, tmax, t_out, al, be);
+    }
     const float num = nD.w - fmaf(nD.z, o.z, fmaf(nD.y, o.y, nD.x * o.x));
     const float t = __fdividef(num, denom);
-    if (!(tmin <= t && t <= tmax)) return false;
+    // the same margin on t's interval: a hit within 1e-6 (relative) of tmin or of the closest hit so far is the reference's call
+    if (!(tmin * (1.0f - kTieEps) <= t && t <= tmax * (1.0f + kTieEps))) return false;
+    const bool t_clear = tmin * (1.0f + kTieEps) <= t && t <= tmax * (1.0f - kTieEps);
     const float4 A = __ldg(q + 1), B = __ldg(q + 2);
     const float ao = fmaf(A.z, o.z, fmaf(A.y, o.y, A.x * o.x)), ad = fmaf(A.z, d.z, fmaf(A.y, d.y, A.x * d.x));
     const float bo = fmaf(B.z, o.z, fmaf(B.y, o.y, B.x * o.x)), bd = fmaf(B.z, d.z, fmaf(B.y, d.y, B.x * d.x));
     const float alpha = fmaf(t, ad, ao) - A.w, beta = fmaf(t, bd, bo) - B.w;
     const int type = __float_as_int(A.w) & 3;
+    // m > 0: inside by more than the margin; m < 0: outside by more than the margin; else undecided
+    float m;
     if (type == 0) {
-        if (!(0.0f <= alpha && alpha <= 1.0f) || !(0.0f <= beta && beta <= 1.0f)) return false;
+        m = fminf(fminf(alpha, 1.0f - alpha), fminf(beta, 1.0f - beta));
     } else if (type == 1) {
         const float da = alpha - 0.5f, db = beta - 0.5f;
-        if (fmaf(da, da, db * db) > 0.25f) return false;
+        m = 0.25f - fmaf(da, da, db * db);
     } else {
-        if (alpha < 0.0f || beta < 0.0f || alpha + beta > 1.0f) return false;
+        m = fminf(fminf(alpha, beta), 1.0f - (alpha + beta));
     }
-    t_out = t;
-    return true;
+    if (m > kEdgeEps && t_clear) {
+        t_out = t;
+        return true;
+    }
+    if (m < -kEdgeEps) return false;
+    float al, be;
+    return plane_t<false>(o, d, p, tmin, tmax, t_out, al, be);
 }
 
 // ---- traversal ----------------------------------------------------------------------------------------------
@@ -400,7 +417,7 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
         } else {
             if (COUNT) wc.planes++;
 #if RTB_FAST_PLANE
-            if (!X) h = plane_fast_t(r.o, r.d, sc.planes_fast + 3 * (size_t)(first + k), r.tmin, r.closest, t);
+            if (!X) h = plane_fast_t(r.o, r.d, sc.planes_fast + 3 * (size_t)(first + k), sc.planes + 5 * (size_t)(first + k), r.tmin, r.closest, t);
             else
 #endif
             h = plane_t<X>(r.o, r.d, sc.planes + 5 * (size_t)(first + k), r.tmin, r.closest, t, al, be);

@@ -15,6 +15,7 @@ MAX_REL_T = 1e-5            # on rays whose ids agree
 ID_BUDGET_FAST = 1e-5       # fraction of rays whose production-arithmetic id may differ from the reference's BVH walk ...
 ID_BUDGET_REFWALK = 2e-4    # ... and from it in exact mode: the reference's own slab test culls grazing hits its leaf test accepts
 NEAR_TIE_REL = 1e-4         # a mismatch is a "near tie" when the two hits' t agree to this
+SCAN_PHANTOM_BUDGET = {10000: 2e-4, 100000: 5e-4, 1000000: 4e-3}   # vs the exhaustive scan: phantom grazing hits outside the boxes
 
 
 def _classify(rays, ty, ix, t, oy, oi, orec, sp):
@@ -66,12 +67,14 @@ def test_production_and_exact_ids_t_full_1080p(rt, orc, n):
         ok = ~mism_lin & (ly >= 0)
         rel = np.abs(t[sel][ok] - lrec[ok, 0]) / lrec[ok, 0]
         print("n=%d %s: vs linear scan %d / %d ids differ, max rel dt %.3g; " % (n, name, mism_lin.sum(), len(sel), rel.max()), end="")
+        # The exhaustive scan is NOT what the reference renders with (its hit_scene walks the BVH), and it reports hits the
+        # reference's own tree never reaches: the fp32 discriminant of a small distant sphere carries an absolute rounding error
+        # of ~1e-4 |d|^2, so the leaf test accepts rays that pass OUTSIDE the sphere -- and outside its box -- by up to ~1e-2
+        # (radius 0.0135 at 1M spheres: 1.4e-3 of the rays; 1e-4 at 100k; none at 10k).  Every difference must be of that class.
+        tie, graze, other = _classify(rays[sel], ty[sel], ix[sel], t[sel], ly, li, lrec, sp)
+        assert other == 0 and mism_lin.mean() <= SCAN_PHANTOM_BUDGET[n]
         if exact:
-            assert mism_lin.sum() == 0
             assert (bits(t[sel][ok]) == bits(lrec[ok, 0])).all()       # bit-equal t
-        else:
-            tie, graze, other = _classify(rays[sel], ty[sel], ix[sel], t[sel], ly, li, lrec, sp)
-            assert other == 0 and mism_lin.mean() <= 1e-3              # (one ray of the sample is 1e-4)
         assert rel.max() <= MAX_REL_T
         # ---- vs the reference's BVH walk, every ray
         mism = (ty != by) | (ix != bi)
@@ -156,7 +159,8 @@ def test_image_vs_reference_cuda_render_10k(rt, ref):
 def _quad_scene(rt):
     """a textured Lambertian quad seen head-on inside a huge emissive sphere: every sample's radiance is exactly the texture
     value at its hit point (one bounce off the quad, then the light), so a 1-spp frame IS a picture of the texture filter"""
-    pl = rt.make_planes([[-2, -1.5, -3]], [[4, 0, 0]], [[0, 3, 0]], 0, rt.QUAD)
+    # the reference camera's up vector is +z (src/camera.cu:171-196), so the view direction must not be: look along +x
+    pl = rt.make_planes([[3, -2, -1.5]], [[0, 4, 0]], [[0, 0, 3]], 0, rt.QUAD)
     sp = np.zeros(1, rt.SPHERE)
     sp["center"], sp["radius"], sp["material_idx"] = [[0, 0, 0]], 1000.0, 1
     mt = np.zeros(2, rt.MATERIAL)
@@ -166,7 +170,7 @@ def _quad_scene(rt):
     rng = np.random.default_rng(5)
     tex = np.ones((48, 64, 4), np.float32)
     tex[..., :3] = rng.random((48, 64, 3), dtype=np.float32)
-    cam = rt.build_camera(192, 256, [0, 0, 0], [0, 0, -3], 50.0, 1, 4)   # the quad fills the view: ~4 pixels per texel
+    cam = rt.build_camera(192, 256, [0, 0, 0], [3, 0, 0], 50.0, 1, 4)    # the quad fills the view: ~4 pixels per texel
     return sp, pl, mt, tex, cam
 
 
@@ -184,13 +188,22 @@ def test_texture_unit_pinned_to_reference_kernel(rt, orc, ref):
     fg, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_GPU)
     sc.close()
     q = 1.0 / 256                                               # one quantum of the unit's 8-bit filter weights x texel contrast <= 1
-    for name, f in (("oracle restatement", fo), ("RT_TEX_GPU", fg)):
-        d = np.abs(f - fr)
-        print("%s vs reference kernel: max |diff| %.3g, 99th pct %.3g, mean %.3g (CPU-convention image: mean |diff| %.3g)"
-              % (name, d.max(), np.percentile(d, 99), d.mean(), np.abs(f_cpu - fr).mean()))
-        # the reference kernel contracts FMAs, so (u, v) differ from the host build's by ulps: a weight may flip by one quantum
-        assert d.max() <= 2 * q + 1e-5 and np.percentile(d, 99) <= q + 1e-5 and d.mean() <= 0.1 * q
-    assert np.abs(f_cpu - fr).mean() > 20 * np.abs(fo - fr).mean()    # and it is NOT the CPU convention (V flip, no half texel)
+    d_cpu = np.abs(f_cpu - fr).mean()
+    # (2) the library's texture-unit path IS the reference kernel's: same unit, same descriptor.  The reference kernel contracts
+    #     FMAs, so (u, v) differ from the exact policy's by ulps and a filter weight may flip by one quantum on a few pixels
+    d = np.abs(fg - fr)
+    print("RT_TEX_GPU vs reference kernel: max |diff| %.3g, 99th pct %.3g, mean %.3g" % (d.max(), np.percentile(d, 99), d.mean()))
+    assert d.max() <= 2 * q + 1e-5 and np.percentile(d, 99) <= 1e-5 and d.mean() <= 1e-5
+    # (1) the oracle's CPU restatement.  Measured (profiles/r02_texture_unit_fit.txt): the unit's output is NOT an exact
+    #     blend of the fp32 texels -- even the best pair of 8-bit weights per pixel leaves a median residual of 5e-4 (about 10-11
+    #     bits: the filter datapath is narrower than fp32) -- so no CPU formula reproduces it bit for bit.  Of the candidate
+    #     rules (full-precision weights 6.5e-4, weights truncated to 8 bits 1.1e-3, rounded to 9 bits 7.1e-4) the restatement's
+    #     "weights rounded to 8 bits" fits best: mean 4.6e-4, 99th percentile 2.1e-3, max 4.9e-3.
+    d = np.abs(fo - fr)
+    print("oracle restatement vs reference kernel: max |diff| %.3g, 99th pct %.3g, mean %.3g (CPU-convention image: mean |diff| %.3g)"
+          % (d.max(), np.percentile(d, 99), d.mean(), d_cpu))
+    assert d.max() <= 2 * q + 1e-5 and np.percentile(d, 99) <= q + 1e-5 and d.mean() <= 1e-3
+    assert d_cpu > 100 * d.mean()                                # and neither is the CPU convention (V flip, no half texel)
 
 
 def test_textured_spheres_exact_mode_matches_the_reference_frame(rt):
@@ -242,6 +255,7 @@ def test_scene_handle_is_usable_from_any_thread_and_device(rt):
 
 def _render_tiles_threads(rt, n, sp, pl, mt, cam, **kw):
     """n ranks as n threads of this process (rt_comm_init_all), rank i on device i % device_count"""
+    import torch  # noqa: F401  -- first, so that the library binds the libnccl torch brings (one NCCL per process)
     ndev = rt.device_count()
     devs = [i % ndev for i in range(n)]
     if len(set(devs)) < n:
@@ -362,6 +376,7 @@ def test_driver_split_tiles_writes_the_single_gpu_files(rt, tmp_path, n):
     """rt_main --gpus n --split tiles: every frame rendered by n devices together; same bytes on disk as one device"""
     if rt.device_count() < n:
         pytest.skip("needs %d GPUs" % n)
+    import torch  # noqa: F401  -- see _render_tiles_threads
     outs = {}
     for tag, kw in (("one", dict(gpus=1)), ("tiles", dict(gpus=n, split_tiles=True))):
         (tmp_path / tag).mkdir()

@@ -30,6 +30,17 @@ def test_c_abi_exports_every_declared_symbol(rt):
     assert b"sm_100a" in rt.lib().rt_version()
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/include"), reason="needs the reference's headers")
+def test_integration_patch_compiles_against_the_reference(tmp_path):
+    """INTEGRATION.md section 2 is not pseudo-code: the patch compiles against the reference's unmodified headers, and the
+    document carries the file verbatim"""
+    import subprocess
+    src = os.path.join(ROOT, "tools", "integration", "camera_render_patch.cu")
+    subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-std=c++17", "-c", "-w", "-I/root/reference/include", "-I" + os.path.join(ROOT, "include"),
+                           "-o", str(tmp_path / "patch.o"), src])
+    assert open(src).read() in open(os.path.join(ROOT, "INTEGRATION.md")).read()
+
+
 def test_struct_sizes_match_header(rt):
     assert C.sizeof(rt.RenderOpts) == 56 and C.sizeof(rt.WorkCounters) == 48
     assert C.sizeof(rt.TraceOpts) == 8 and C.sizeof(rt.TilesInfo) == 56 and rt.COMM_ID_BYTES == 128
