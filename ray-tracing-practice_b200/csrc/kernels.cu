@@ -56,6 +56,10 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
     // warp-uniform tile pool
     int pool_x0 = 0, pool_y0 = 0, pool_chunk = 0, pool_next = kBlockPixels;
     bool exhausted = false;
+    unsigned queue;  // the work queue this warp draws from: its SM's, until that one is dry
+    if (fp.queue_per_cta) queue = blockIdx.x;
+    else asm("mov.u32 %0, %%smid;" : "=r"(queue));
+    queue %= (unsigned)fp.nqueues;
 
     // per-lane state
     RayTrav rt;
@@ -106,19 +110,29 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             unsigned need = __ballot_sync(full, rt.ref == kRefNeed && !has_pixel);
             while (need && !exhausted) {
                 if (pool_next >= kBlockPixels) {
-                    unsigned k = 0;
-                    if (lane == 0) k = atomicAdd(fp.tile_counter, 1u);
-                    k = __shfl_sync(full, k, 0);
-                    // item = (tile, 8x4 block, sample chunk); chunk fastest by default: the chunks of a block are in flight
-                    // together, on many SMs, and find the block's part of the tree in L2
+                    // item = (tile, 8x4 block, sample chunk), chunk fastest: the chunks of a block are in flight together and
+                    // find the block's part of the tree in cache.  Queue q holds the blocks kb = j * nqueues + q.
                     const unsigned per_chunk = (unsigned)fp.my_tiles * kBlocksPerTile;
-                    if (k >= per_chunk * (unsigned)nchunks) { exhausted = true; break; }
-                    const unsigned kb = fp.chunk_major ? k % per_chunk : k / (unsigned)nchunks;
+                    const unsigned nq = (unsigned)fp.nqueues;
+                    unsigned k = 0xffffffffu;
+                    if (lane == 0) {
+                        for (unsigned tries = 0; tries < nq; ++tries) {
+                            const unsigned mine = (per_chunk + nq - 1u - queue) / nq * (unsigned)nchunks;  // items of this queue
+                            const unsigned got = atomicAdd(fp.tile_counter + queue * kQueueStride, 1u);
+                            if (got < mine) { k = got; break; }
+                            queue = queue + 1u == nq ? 0u : queue + 1u;   // dry: steal from the next queue (and stay there)
+                        }
+                    }
+                    k = __shfl_sync(full, k, 0);
+                    queue = __shfl_sync(full, queue, 0);
+                    if (k == 0xffffffffu) { exhausted = true; break; }
+                    const unsigned kb = fp.chunk_major ? (k % ((per_chunk + nq - 1u - queue) / nq)) * nq + queue
+                                                       : (k / (unsigned)nchunks) * nq + queue;
                     const int tile = tile_of_rank((int)(kb / kBlocksPerTile), fp.tile_rank, fp.tile_nranks);  // >= tile count: no pixels
                     const int blk = (int)(kb % kBlocksPerTile);  // 8 blocks of 8x4 pixels inside the 16x16 tile
                     pool_x0 = (tile % fp.tiles_x) * kTile + (blk & 1) * 8;
                     pool_y0 = (tile / fp.tiles_x) * kTile + (blk >> 1) * 4;
-                    pool_chunk = (int)(fp.chunk_major ? k / per_chunk : k % (unsigned)nchunks);
+                    pool_chunk = (int)(fp.chunk_major ? k / ((per_chunk + nq - 1u - queue) / nq) : k % (unsigned)nchunks);
                     pool_next = 0;
                 }
                 int avail = kBlockPixels - pool_next;

@@ -23,7 +23,13 @@ struct FrameParams {
     long long* acc;
     int chunk_spp, nchunks;
     int chunk_major;                  // item order: 0 = (block, chunk) chunk fastest; 1 = all blocks of chunk 0, then chunk 1, ...
-    unsigned int* tile_counter;       // work queue head (zeroed before launch)
+    // Work queues (zeroed before launch): nqueues heads, kQueueStride words apart.  render_mega: queue q owns the 8x4 blocks
+    // kb with kb % nqueues == q; an SM's warps draw from queue smid % nqueues and move on to the next queue when theirs runs
+    // dry, so that the warps of one SM work on the SAME block (its sample chunks) at the same time and share its part of the
+    // tree in L1.  nqueues == 1 is the single global queue (the other kernels use head 0 only).
+    unsigned int* tile_counter;
+    int nqueues;
+    int queue_per_cta;                // 1: a warp's home queue is blockIdx.x % nqueues instead of smid % nqueues
     unsigned long long* counters;     // 6 x u64: segments,nodes,spheres,planes,hits,samples
 };
 
@@ -34,6 +40,8 @@ struct LaunchCfg {
 };
 
 constexpr int kTile = 16;  // == RT_TILE
+constexpr int kQueueStride = 16;  // 64 bytes between queue heads
+constexpr int kMaxQueues = 1024;
 
 // Interleaved-tile partition of a frame over `nranks` devices.  Tiles (row-major ids) are dealt in groups of nranks
 // consecutive ids, one tile of every group to every rank; WHICH tile of group g a rank gets is rotated by a hash of g.

@@ -177,7 +177,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         s->dev.tex_h = th;
     }
     auto chk2 = [&](cudaError_t e) { if (e != cudaSuccess) { cudaGetLastError(); fail(RT_ERR_CUDA, cudaGetErrorString(e)); return 1; } return 0; };
-    if (chk2(cudaMalloc((void**)&s->d_tile_counter, 64)) || chk2(cudaMalloc((void**)&s->d_counters, 64)) ||
+    if (chk2(cudaMalloc((void**)&s->d_tile_counter, kMaxQueues * kQueueStride * sizeof(unsigned int))) || chk2(cudaMalloc((void**)&s->d_counters, 64)) ||
         chk2(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) || chk2(cudaEventCreate(&s->ev0)) ||
         chk2(cudaEventCreate(&s->ev1)) || chk2(cudaEventCreate(&s->ev2)))
         return bail(RT_ERR_CUDA);
@@ -355,6 +355,12 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     fp.my_tiles = (tiles + o.tile_nranks - 1) / o.tile_nranks;  // groups of the interleave; a rank's slot in the last one may be empty
     fp.fb = d_fb;
     fp.tile_counter = s->d_tile_counter;
+    fp.nqueues = s->num_sms < kMaxQueues ? s->num_sms : kMaxQueues;  // one queue per SM (render_mega)
+    if (const char* e = getenv("RTB_QUEUES")) fp.nqueues = atoi(e);
+    fp.queue_per_cta = 0;
+    if (const char* e = getenv("RTB_QUEUE_PER_CTA")) fp.queue_per_cta = atoi(e) ? 1 : 0;
+    if (fp.nqueues < 1) fp.nqueues = 1;
+    if (fp.nqueues > kMaxQueues) fp.nqueues = kMaxQueues;
     fp.counters = s->d_counters;
     // sample chunks: work items of a few samples (the tail is what limits strong scaling over GPUs, and short items keep a
     // warp's lanes on the same few pixels and in step: measured, items of 171 samples render the headline frame 6 % slower
@@ -408,7 +414,7 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     if (const char* e = getenv("RTB_PARK_MIN")) fp.park_min = atoi(e);
     if (fp.refill_min < 1) fp.refill_min = 1;
     if (fp.park_min < 1) fp.park_min = 1;
-    RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, 64, stream));
+    RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, kMaxQueues * kQueueStride * sizeof(unsigned int), stream));
     RT_CUDA(cudaMemsetAsync(s->d_counters, 0, 64, stream));
     RT_CUDA(cudaEventRecord(s->ev0, stream));
     if (fp.acc) RT_CUDA(cudaMemsetAsync(fp.acc, 0, (size_t)fp.cam.W * fp.cam.H * 3 * sizeof(long long), stream));  // inside the timed region

@@ -36,14 +36,14 @@ def main():
             t0 = time.perf_counter()
             r = subprocess.run([exe] + flags, input=cfg.encode(), capture_output=True, timeout=3000)
             wall = time.perf_counter() - t0
-            lines = [l.split("\t") for l in r.stdout.decode().strip().split("\n") if l.strip()]
+            lines = [l.split("\t") for l in r.stdout.decode().strip().split("\n") if l.count("\t") == 2]
             ms = np.array([float(l[1]) for l in lines]) if lines else np.zeros(0)
             files = len([f for f in os.listdir(td) if f.startswith("render_")])
             print(json.dumps(dict(run=tag, flags=flags, rc=r.returncode, frames=a.frames, files_written=files, wall_s=wall,
                                   ms_per_frame_wall=1e3 * wall / max(a.frames, 1), frame_ms_printed_mean=float(ms.mean()) if len(ms) else None,
                                   frame_ms_printed_max=float(ms.max()) if len(ms) else None, width=1080, height=720, spp=a.sqrt_spp ** 2,
                                   max_depth=50, texture="none (../floor2.jpg of the shipped config is not shipped, SURVEY Q6)",
-                                  stderr=r.stderr.decode()[-200:])), flush=True)
+                                  stdout_lines=len(r.stdout.decode().split("\n")), stderr=r.stderr.decode()[-300:])), flush=True)
     if a.ref:
         from oracle import oracle_py as O
         if O.ref_available():
