@@ -140,6 +140,20 @@ typedef struct rt_trace_opts {
 int rt_trace_primary_ex(rt_scene* scene, const float* rays6, int num_rays, float tmin, float tmax, const rt_trace_opts* opts,
                         int* prim_type, int* prim_index, float* t);
 
+/* ---- allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel, same
+ * arguments and same results as rt_trace_primary_ex, but the device staging area for the rays and the results is a
+ * file-scope `static __device__` array (csrc/rt_noalloc.cu) instead of a cudaMalloc'ed buffer: the call performs no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  Limits: num_rays <= RT_NOALLOC_MAX_RAYS (more is rejected
+ * with RT_ERR_INVALID and a message naming the limit); the array is RT_NOALLOC_MAX_RAYS x 36 bytes = 9 MiB per GPU that
+ * loads the library, held until the process exits; every call on a GPU shares it, so calls that overlap on one GPU race and
+ * must be serialised by the caller.  The array keeps the last call's contents; the call overwrites every slot it reads, so
+ * nothing has to be cleared. */
+#define RT_NOALLOC_MAX_RAYS 262144
+int rt_trace_primary_noalloc(rt_scene* scene, const float* rays6, int num_rays, float tmin, float tmax, const rt_trace_opts* opts,
+                             int* prim_type, int* prim_index, float* t);
+int rt_noalloc_max_rays(void); /* = RT_NOALLOC_MAX_RAYS of the library as built */
+
 /* Device-side output stage replacing ISaver::writeColor's arithmetic (src/camera.cu:136-148): byte =
  * (unsigned char)(256*clamp(sqrt(sum/divisor),0,0.999)).  d_fb_sum_rgb is a device pointer, rgb_u8 a host one. */
 int rt_tonemap_u8(rt_scene* scene, const void* d_fb_sum_rgb, int width, int height, int divisor, unsigned char* rgb_u8);

@@ -39,7 +39,8 @@ BVH_HOST_SAH, BVH_GPU_LBVH = 0, 1
 TILE = 16
 
 C_ABI_SYMBOLS = ["rt_scene_create", "rt_scene_create_ex", "rt_scene_rebuild", "rt_scene_destroy", "rt_scene_get_stats", "rt_render", "rt_render_device",
-                 "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_trace_primary_ex", "rt_tonemap_u8", "rt_tiles_pack",
+                 "rt_render_finish", "rt_render_u8", "rt_trace_primary", "rt_trace_primary_ex", "rt_trace_primary_noalloc",
+                 "rt_noalloc_max_rays", "rt_tonemap_u8", "rt_tiles_pack",
                  "rt_tiles_unpack", "rt_tiles_packed_floats", "rt_tile_owner", "rt_comm_unique_id", "rt_comm_init_rank",
                  "rt_comm_init_all", "rt_comm_destroy", "rt_comm_rank", "rt_comm_size", "rt_render_tiles", "rt_last_error",
                  "rt_device_count", "rt_set_device", "rt_version"]
@@ -114,6 +115,7 @@ def lib():
         L.rt_render_u8.argtypes = [vp, vp, vp, ci, vp, vp, vp]
         L.rt_trace_primary.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp]
         L.rt_trace_primary_ex.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp, vp]
+        L.rt_trace_primary_noalloc.argtypes = [vp, vp, ci, cf, cf, vp, vp, vp, vp]
         L.rt_tile_owner.restype = None
         L.rt_tile_owner.argtypes = [ci, ci, vp, vp]
         L.rt_comm_unique_id.argtypes = [vp]
@@ -384,6 +386,16 @@ class Scene:
         else:
             to = TraceOpts(C.sizeof(TraceOpts), 0)
             _check(lib().rt_trace_primary_ex(self.h, _ptr(rays), n, tmin, tmax, C.byref(to), _ptr(typ), _ptr(idx), _ptr(t)))
+        return typ, idx, t
+
+    def trace_primary_noalloc(self, rays6, tmin=0.001, tmax=1e30, exact=True, out=None):
+        """rt_trace_primary_noalloc: as trace_primary, staged through the library's static device array (no cudaMalloc in the
+        call; at most rt_noalloc_max_rays() rays).  out = (type, index, t) arrays to fill, so a caller's loop allocates nothing"""
+        rays = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = len(rays)
+        typ, idx, t = out if out is not None else (np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float32))
+        to = TraceOpts(C.sizeof(TraceOpts), 1 if exact else 0)
+        _check(lib().rt_trace_primary_noalloc(self.h, _ptr(rays), n, tmin, tmax, C.byref(to), _ptr(typ), _ptr(idx), _ptr(t)))
         return typ, idx, t
 
     def render_tiles(self, comm, cam, out=None, want_host=True, **kw):
