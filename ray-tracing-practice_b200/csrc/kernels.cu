@@ -167,7 +167,18 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     rt.ref = kRefIdle;
                 }
             }
+#if RTB_LOOP_SHAPE == 4
+            // time-sliced TRACE: a lane may arrive here in the middle of a traversal (it keeps ref, sp, closest and the hit so
+            // far; its stack is in local memory).  The constants derived from (o, d) are recomputed for EVERY lane -- the same
+            // values for a resumed ray -- so none of them is live across the shading code above.
+            trav_setup<X>(rt, ps.o, ps.d, 0.001f);
+            if (start_ray) {
+                trav_reset(rt, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
+                for (int k = 0; k < sc.num_hoisted; ++k) trav_leaf<X, COUNT>(sc, rt, wc, sc.hoisted[k]);
+            }
+#else
             if (start_ray) trav_begin<X, COUNT>(sc, rt, ps.o, ps.d, 0.001f, 1e30f, wc);  // Interval(0.001f, 1e30f), src/camera.cu:226
+#endif
         }
         if (__all_sync(full, rt.ref == kRefIdle)) break;  // no pixels left for any lane
         // ================= TRACE phase: every lane runs its segment's closest-hit traversal to completion (traverse.cuh).
@@ -176,6 +187,19 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         // that batch the leaf tests, lanes waiting for each other, and postponed leaves (below) all cost more than they save.
 #if RTB_LOOP_SHAPE == 1
         while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
+            if (ref_is_leaf(rt.ref)) trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
+            if (ref_is_inner(rt.ref)) {
+                if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
+            }
+        }
+#elif RTB_LOOP_SHAPE == 4
+        // time-sliced: the phase ends as soon as fewer than trace_min lanes are still traversing and some lane waits to be
+        // shaded.  The unfinished lanes sit out the SHADE phase (predicated off) and resume here, next to the fresh rays of
+        // the others -- the traversal runs with more lanes per instruction, the shading code runs more often.
+        for (;;) {
+            const unsigned am = __ballot_sync(full, ref_is_leaf(rt.ref) || ref_is_inner(rt.ref));
+            if (am == 0u) break;
+            if (__popc(am) < fp.trace_min && __any_sync(full, rt.ref == kRefDone)) break;
             if (ref_is_leaf(rt.ref)) trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
             if (ref_is_inner(rt.ref)) {
                 if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);

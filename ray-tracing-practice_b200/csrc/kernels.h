@@ -13,8 +13,10 @@ struct FrameParams {
     int tex_mode;       // 0 cpu semantics, 1 texture unit
     int tile_rank, tile_nranks;
     int tiles_x, tiles_y, my_tiles;
+    int trace_min;                    // render_mega, time-sliced TRACE (RTB_LOOP_SHAPE 4): the phase ends when fewer lanes are traversing
     int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
     int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
+    int regroup;                      // pooled megakernel: 1 = order the parked hits by material class before a shading pass (mega_pool.cu)
     float* fb;                        // W*H*3 sums
     // sample chunks (render_mega only): a work item is (8x4 pixel block, chunk of chunk_spp samples).  With nchunks > 1 a lane
     // adds its chunk's partial sum to the pixel's 64-bit FIXED-POINT accumulator acc[pixel][channel] (value * 2^32, one
@@ -49,8 +51,18 @@ constexpr int kMaxQueues = 1024;
 // 120 tiles at 1080p, 480 at 8K, for 2 / 4 / 8 ranks -- i.e. vertical stripes, and a rank's cost then follows whatever
 // the picture holds in its stripes.)  k = the rank's k-th tile = group index; rank r's packed buffer holds its tiles in
 // increasing k.  The last group may be short: a (k, rank) whose tile id is >= the tile count owns nothing.
+#ifndef RTB_TILE_ROT
+#define RTB_TILE_ROT 1
+#endif
 __host__ __device__ inline int tile_rot(unsigned int g, int nranks) {
-    return nranks > 1 ? (int)(((g * 0x9E3779B1u) >> 16) % (unsigned int)nranks) : 0;
+#if RTB_TILE_ROT == 1
+    // floor(frac(g * golden ratio) * nranks): the TOP bits of the 32-bit product are the Kronecker (golden-ratio) sequence,
+    // which is low-discrepancy in g -- over ANY run of consecutive groups every rank gets every position of the group almost
+    // equally often, so a cost that varies smoothly along the rows cancels instead of adding up as a random walk
+    return nranks > 1 ? (int)(((unsigned long long)(g * 0x9E3779B9u) * (unsigned long long)nranks) >> 32) : 0;
+#else
+    return nranks > 1 ? (int)(((g * 0x9E3779B1u) >> 16) % (unsigned int)nranks) : 0;  // a hash of g: pseudo-random positions
+#endif
 }
 __host__ __device__ inline int tile_of_rank(int k, int rank, int nranks) {
     int p = rank - tile_rot((unsigned int)k, nranks);

@@ -123,6 +123,45 @@ __device__ __forceinline__ void shade_pass(const DevScene& sc, const FrameParams
     __syncwarp();
 }
 
+// north_star subsystem 3, "regroup by material after a bounce" (the divergent switch it targets is material_scatter's,
+// include/materials.h:70-140): when more hits are parked than one shading pass takes, the hit queue (<= kPool = 64 entries,
+// two per lane) is stably ordered by the class of what was hit -- miss, LAMBERTIAN, METAL, DIELECTRIC, DIFFUSE_LIGHT -- with
+// one ballot-ranked counting sort, so that the 32 hits of a pass fall into as few branches of shade_vertex as possible.
+// Which hits share a pass changes nothing in the image: every slot's sample stream is its own.
+__device__ __forceinline__ void regroup_hits_by_material(const DevScene& sc, const WarpPool& wp, WarpSched& ws, int lane) {
+    const unsigned full = 0xffffffffu, lt = (1u << lane) - 1u;
+    int e[2], c[2], r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int q = lane + 32 * h;
+        e[h] = q < ws.hit_cnt ? wp.in(kFHitQ, (ws.hit_head + q) & (kPool - 1)) : -1;
+        c[h] = 7;
+        if (e[h] >= 0) {
+            const int href = wp.in(kFHitRef, e[h]);
+            c[h] = 0;
+            if (href >= 0) {
+                const int slot = href & 0x3fffffff;
+                const int mat = (href >> 30) == 0 ? __ldg(sc.sphere_meta + slot).x : __float_as_int(__ldg(sc.planes + 5 * (size_t)slot + 2).w);
+                c[h] = 1 + __float_as_int(__ldg(sc.mats + 3 * (size_t)mat).w);
+            }
+        }
+        r[h] = 0;
+    }
+    int base = 0;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        const unsigned m0 = __ballot_sync(full, c[0] == k), m1 = __ballot_sync(full, c[1] == k);
+        if (c[0] == k) r[0] = base + __popc(m0 & lt);
+        if (c[1] == k) r[1] = base + __popc(m0) + __popc(m1 & lt);
+        base += __popc(m0) + __popc(m1);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+        if (e[h] >= 0) wp.in(kFHitQ, (ws.hit_head + r[h]) & (kPool - 1)) = e[h];
+    __syncwarp();
+}
+
 template <int MODE, bool X, bool COUNT>
 __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(const __grid_constant__ DevScene sc,
                                                                                 const __grid_constant__ FrameParams fp) {
@@ -182,6 +221,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(co
         // ---- SHADE: a full warp of parked hits, or whatever is parked when lanes starve
         const unsigned starve = __ballot_sync(full, rt.ref == kRefIdle);
         if (ws.hit_cnt >= park_min || (ws.hit_cnt > 0 && ws.ready_cnt == 0 && starve != 0u)) {
+            if (fp.regroup && ws.hit_cnt > 32) regroup_hits_by_material(sc, wp, ws, lane);
             const int n = min(ws.hit_cnt, 32);
             const int s = wp.in(kFHitQ, (ws.hit_head + lane) & (kPool - 1));
             ws.hit_head = (ws.hit_head + n) & (kPool - 1);

@@ -412,6 +412,10 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     fp.park_min = 32;
     if (const char* e = getenv("RTB_REFILL_MIN")) fp.refill_min = atoi(e);
     if (const char* e = getenv("RTB_PARK_MIN")) fp.park_min = atoi(e);
+    fp.trace_min = 16;
+    if (const char* e = getenv("RTB_TRACE_MIN")) fp.trace_min = atoi(e);
+    fp.regroup = 0;
+    if (const char* e = getenv("RTB_POOL_REGROUP")) fp.regroup = atoi(e) ? 1 : 0;
     if (fp.refill_min < 1) fp.refill_min = 1;
     if (fp.park_min < 1) fp.park_min = 1;
     RT_CUDA(cudaMemsetAsync(s->d_tile_counter, 0, kMaxQueues * kQueueStride * sizeof(unsigned int), stream));

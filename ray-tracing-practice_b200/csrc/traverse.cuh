@@ -267,8 +267,10 @@ struct TravStack {
     }
 };
 
+// the per-ray constants of a segment (everything RayTrav derives from o, d): a pure function of (o, d), so a scheduler may
+// drop them and call this again for a traversal it resumes (render_mega's time-sliced TRACE phase does)
 template <bool X>
-__device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, float tmax) {
+__device__ __forceinline__ void trav_setup(RayTrav& r, V3 o, V3 d, float tmin) {
     const float eps = 1e-20f;
     float dx = fabsf(d.x) < eps ? copysignf(eps, d.x) : d.x;
     float dy = fabsf(d.y) < eps ? copysignf(eps, d.y) : d.y;
@@ -289,7 +291,6 @@ __device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, fl
     r.inv_a = X ? 0.0f : 1.0f / r.a;
 #endif
     r.tmin = tmin;
-    r.closest = tmax;
     // conservative slab test: the far side is widened by a few ulps of the slab products (boxes are padded too)
     // Each axis contributes the rounding error of its own slab products, CAPPED: for an axis the ray is (almost) parallel
     // to, id = 1e20 and o*id = 1e21 -- its products decide nothing unless the origin sits within 1e-6 of a box face, but
@@ -299,12 +300,23 @@ __device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, fl
     r.nx = dx < 0.0f ? 3 : 0;
     r.ny = dy < 0.0f ? 4 : 1;
     r.nz = dz < 0.0f ? 5 : 2;
+}
+
+// start of a traversal: nothing hit, at the root, empty stack
+__device__ __forceinline__ void trav_reset(RayTrav& r, float tmax) {
+    r.closest = tmax;
     r.ref = 0;  // root
     r.sp = 0;
     r.htype = -1;
     r.hslot = -1;
     r.horig = -1;
     r.best_key = 0;
+}
+
+template <bool X>
+__device__ __forceinline__ void trav_init(RayTrav& r, V3 o, V3 d, float tmin, float tmax) {
+    trav_setup<X>(r, o, d, tmin);
+    trav_reset(r, tmax);
 }
 
 // pops entries until one starts no further than the closest hit; kRefDone when the stack runs out

@@ -25,7 +25,7 @@ def packed_floats(W, H, world):
 
 def tile_rot(g, world):
     """position rotation of tile group g (kernels.h: tile_rot)"""
-    return (((g * 0x9E3779B1) & 0xFFFFFFFF) >> 16) % world if world > 1 else 0
+    return (((g * 0x9E3779B9) & 0xFFFFFFFF) * world) >> 32 if world > 1 else 0
 
 
 def tile_of_rank(k, rank, world):
