@@ -260,6 +260,8 @@ class Ref(_Checker):
         L.ref_gpu_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.ref_selfcheck_color.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.ref_cpu_render_config.argtypes = [C.c_void_p]
+        if hasattr(L, "ref_gpu_render_config"):
+            L.ref_gpu_render_config.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.ref_render_cpu_unmodified.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_int,
                                                 C.c_int, C.c_void_p]
 
@@ -319,6 +321,16 @@ class _RefConfigScene(_Scene):
         f(self.h, o)
         fov = np.frombuffer(bytes(o), np.float32)[5]
         return dict(W=o[0], H=o[1], max_depth=o[2], sqrt_spp=o[3], num_frames=o[4], fov=float(fov))
+
+
+def gpu_render_program_ref(cfg_scene):
+    """The reference program's own gpu_render loop over the config's frames (writes params.output_path); returns the
+    (frame, ms, total_rays) lines it printed."""
+    buf = C.create_string_buffer(1 << 16)
+    rc = cfg_scene.k.lib.ref_gpu_render_config(cfg_scene.h, buf, len(buf))
+    if rc != 0:
+        raise RuntimeError("ref_gpu_render_config failed: %d" % rc)
+    return [(int(a), float(b), int(c)) for a, b, c in (l.split("\t") for l in buf.value.decode().strip().split("\n") if l.count("\t") == 2)]
 
 
 def gpu_render_ref(scene, cam, reps=1):

@@ -504,6 +504,23 @@ int ref_gpu_render(void* h, const void* cam76, int reps, float* fb, float* kerne
     return 0;
 }
 
+// The reference PROGRAM's GPU path for a config scene: its own gpu_render loop (src/camera.cu:290-349) -- per frame the camera
+// of the path, Camera::render (render_kernel + cudaDeviceSynchronize + D2H + the saver's per-pixel writes, :198-215) inside
+// the reference's own event pair -- writing its frames to params.output_path.  The "n\tms\ttotal_rays" lines it prints to
+// std::cout are captured into `out` (the f3 timing baseline).
+int ref_gpu_render_config(void* h, char* out, int cap) {
+    auto* s = (RefScene*)h;
+    if (!s->has_params) return 1;
+    int rc = ref_gpu_prepare(s);
+    if (rc) return rc;
+    std::ostringstream os;
+    std::streambuf* old = std::cout.rdbuf(os.rdbuf());
+    gpu_render(s->params, s->dsd);
+    std::cout.rdbuf(old);
+    if (out && cap > 0) snprintf(out, (size_t)cap, "%s", os.str().c_str());
+    return cudaGetLastError() == cudaSuccess ? 0 : 4;
+}
+
 void ref_scene_destroy(void* h) {
     auto* s = (RefScene*)h;
     if (!s) return;

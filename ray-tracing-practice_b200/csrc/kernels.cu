@@ -10,15 +10,21 @@
 //          max_depth); a lane whose pixel is complete takes the next pixel of the warp's current work item.  Work
 //          items are 8x4-pixel blocks of the 16x16 tiles, fetched with ONE atomicAdd per warp (lane 0) and a shuffle
 //          broadcast; ballot/popc ranks hand the pixels to the lanes that need one.
-//   TRACE  every lane runs the closest-hit traversal of its segment (4-wide BVH, near-first, per-thread stack in local
-//          memory) to completion; the warp re-converges for the next SHADE phase.
-// Measured alternatives that lost and why are in DESIGN.md 4.2: a shared-memory stack, warp votes inside the traversal,
-// lanes leaving the phase early, pre-tracing the next camera ray in idle lanes, and the pooled variant (mega_pool.cu).
+//   TRACE  every lane steps the closest-hit traversal of its segment (4-wide BVH, near-first, per-thread stack in local
+//          memory).  The phase is TIME-SLICED: it ends when fewer than trace_min (6) lanes are still traversing and some lane
+//          waits to be shaded; the unfinished lanes keep ref / sp / closest / the hit so far (their stack is in local memory),
+//          sit out the SHADE phase and resume next to the fresh rays of the others.  The constants derived from (o, d) are
+//          recomputed for every lane after SHADE, so none of them is live across the shading code: 72 registers, no spills,
+//          4 CTAs x 224 threads per SM.  Measured: 180.1 vs 189.9 ms on the headline frame, 267 vs 295 ms on
+//          the reference's shipped scene, against "every lane runs to completion" at 3 x 256 threads and 80 registers.
+// Measured alternatives that lost and why are in DESIGN.md 4.2: a shared-memory stack, warp votes that batch the leaf tests,
+// pre-tracing the next camera ray in idle lanes, a shared-memory lane counter instead of the vote, and the pooled variant
+// (mega_pool.cu).
 // Per-pixel sums are accumulated in registers in sample order (the reference's summation order) and stored once,
 // so the output is deterministic and, in parity mode, comparable bit for bit.
 #include "kernels.h"
 #ifndef RTB_LOOP_SHAPE
-#define RTB_LOOP_SHAPE 1
+#define RTB_LOOP_SHAPE 4
 #endif
 #ifndef RTB_LEAF_K
 #define RTB_LEAF_K 12
@@ -167,7 +173,10 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
                     rt.ref = kRefIdle;
                 }
             }
-#if RTB_LOOP_SHAPE == 4
+#ifndef RTB_SPLIT_SETUP
+#define RTB_SPLIT_SETUP 0
+#endif
+#if RTB_LOOP_SHAPE == 4 || RTB_SPLIT_SETUP
             // time-sliced TRACE: a lane may arrive here in the middle of a traversal (it keeps ref, sp, closest and the hit so
             // far; its stack is in local memory).  The constants derived from (o, d) are recomputed for EVERY lane -- the same
             // values for a resumed ray -- so none of them is live across the shading code above.

@@ -13,7 +13,8 @@ struct FrameParams {
     int tex_mode;       // 0 cpu semantics, 1 texture unit
     int tile_rank, tile_nranks;
     int tiles_x, tiles_y, my_tiles;
-    int trace_min;                    // render_mega, time-sliced TRACE (RTB_LOOP_SHAPE 4): the phase ends when fewer lanes are traversing
+    int trace_min;                    // render_mega, time-sliced TRACE: a TRACE phase ends as soon as fewer than trace_min lanes are still
+                                      // traversing and some lane waits to be shaded (1 = every lane runs to completion)
     int leaf_min;                     // megakernel: lanes that must hold a leaf before the primitive tests run (kernels.cu)
     int refill_min, park_min;         // pooled megakernel: lanes that must be out of rays before a refill; parked hits before a shading pass
     int regroup;                      // pooled megakernel: 1 = order the parked hits by material class before a shading pass (mega_pool.cu)
@@ -77,14 +78,19 @@ __host__ __device__ inline void tile_owner(int t, int nranks, int& rank, int& k)
 // stay the unit of the multi-GPU partition; blocks keep the end-of-frame tail short (8x more, 8x smaller work items).
 constexpr int kBlockPixels = 32;
 constexpr int kBlocksPerTile = kTile * kTile / kBlockPixels;
+// render_mega's launch geometry: 4 CTAs x 224 threads per SM = 28 warps at 72 registers (no spills with the time-sliced TRACE
+// loop).  Measured on the headline frame at trace_min 6: 224x4 180.1 ms, 128x7 180.5, 288x3 181.9 (all 72 registers);
+// 256x4 191.0 and 192x5 193.6 (64 registers, ~120 B of spills); the round-1 geometry 256x3 (80 registers) 192.1.
 #ifndef RTB_MEGA_THREADS
-#define RTB_MEGA_THREADS 256
+#define RTB_MEGA_THREADS 224
 #endif
 #ifndef RTB_MEGA_BLOCKS
-#define RTB_MEGA_BLOCKS 3
+#define RTB_MEGA_BLOCKS 4
 #endif
-constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of the persistent kernels
-constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM they are compiled (register-capped) for
+constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of render_mega
+constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM it is compiled (register-capped) for
+constexpr int kPoolThreads = 256, kPoolBlocksPerSM = 3;  // render_pool / wavefront kernels: the geometry they were measured with
+constexpr int kTraceMinDefault = 6;                 // time-sliced TRACE: see FrameParams::trace_min
 constexpr int kLeafMinDefault = 12;
 
 // persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1

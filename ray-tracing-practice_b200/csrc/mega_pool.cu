@@ -163,7 +163,7 @@ __device__ __forceinline__ void regroup_hits_by_material(const DevScene& sc, con
 }
 
 template <int MODE, bool X, bool COUNT>
-__global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_pool(const __grid_constant__ DevScene sc,
+__global__ void __launch_bounds__(kPoolThreads, kPoolBlocksPerSM) render_pool(const __grid_constant__ DevScene sc,
                                                                                 const __grid_constant__ FrameParams fp) {
     extern __shared__ float4 smem4[];
     const TraversalSmem ts = carve_and_stage(sc, smem4);

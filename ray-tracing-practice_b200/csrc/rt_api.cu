@@ -405,6 +405,7 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     if (top > 1024) top = 1024;
     dev.top_nodes = top;
     LaunchCfg cfg{s->num_sms, kMegaBlocksPerSM, kMegaThreads};
+    if (o.kernel != RT_KERNEL_MEGA) cfg = LaunchCfg{s->num_sms, kPoolBlocksPerSM, kPoolThreads};
     // scheduling thresholds of the megakernels; the RTB_* variables are tuning knobs for profiling runs
     fp.leaf_min = kLeafMinDefault;
     if (const char* e = getenv("RTB_LEAF_MIN")) fp.leaf_min = atoi(e);
@@ -412,7 +413,7 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     fp.park_min = 32;
     if (const char* e = getenv("RTB_REFILL_MIN")) fp.refill_min = atoi(e);
     if (const char* e = getenv("RTB_PARK_MIN")) fp.park_min = atoi(e);
-    fp.trace_min = 16;
+    fp.trace_min = kTraceMinDefault;
     if (const char* e = getenv("RTB_TRACE_MIN")) fp.trace_min = atoi(e);
     fp.regroup = 0;
     if (const char* e = getenv("RTB_POOL_REGROUP")) fp.regroup = atoi(e) ? 1 : 0;

@@ -1,0 +1,16 @@
+#!/bin/bash
+# register-pressure variants: unconditional per-phase setup (77 regs, no spills), 4 CTAs x 256 (64 regs), 4 CTAs x 224 (72 regs)
+cd "$GRAFT_REPO_ROOT" || exit 1
+mkdir -p gpurun_out
+V=$GRAFT_REPO_ROOT/ray-tracing-practice_b200/build
+O=gpurun_out/h_ab.txt; : > $O
+for v in default v_setup v_setup4 v_setup_t224; do
+  if [ $v = default ]; then unset RTB_LIB; else export RTB_LIB=$V/$v.so; fi
+  echo "== $v headline" >> $O; timeout 300 python tools/prof_frame.py --reps 3 >> $O 2>&1
+  echo "== $v shipped" >> $O; timeout 300 python tools/prof_frame.py --workload shipped --reps 2 >> $O 2>&1
+  echo "== $v 1m" >> $O; timeout 300 python tools/prof_frame.py --workload spheres1m_4k_64spp_d8 --reps 2 >> $O 2>&1
+  echo "== $v 10k" >> $O; timeout 300 python tools/prof_frame.py --workload spheres10k_1080p_64spp_d16 --reps 3 >> $O 2>&1
+done
+export RTB_LIB=$V/v_setup.so
+timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -q -x > gpurun_out/h_pytest_setup.log 2>&1; echo "pytest v_setup rc=$?"
+grep -E "^==|kernel_ms" $O | sed 's/"segments.*//' | sed 's/{"workload".*"kernel_ms"/ms/' | paste - - | cut -c1-120
