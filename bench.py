@@ -26,6 +26,19 @@ DEFAULT_WORKLOAD = "spheres100k_1080p_256spp_d32"
 FP32_LANES_PER_SM = 128
 
 
+_RECORD_FD = None
+
+
+def emit(line):
+    """the one JSON line of the run, on the process's original stdout"""
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    if _RECORD_FD is None:
+        os.write(1, data)
+    else:
+        os.write(_RECORD_FD, data)
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -51,7 +64,7 @@ class ClockSampler:
         self.p = None
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "25"], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             pass
 
@@ -139,7 +152,7 @@ def run_reference_arm(args, rank, world):
             "config": {"workload": args.workload, "note": "CPU arm renders a bounded pixel/sample subsample of the workload per step"},
             "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def latest_traffic_profile(workload):
@@ -173,6 +186,13 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    # stdout carries exactly ONE line, the JSON record: native libraries write to fd 1 too (NCCL prints its version banner
+    # there when a communicator is created), so fd 1 points at stderr while the benchmark runs and the record goes to the
+    # saved descriptor
+    global _RECORD_FD
+    sys.stdout.flush()
+    _RECORD_FD = os.dup(1)
+    os.dup2(2, 1)
 
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
@@ -341,7 +361,7 @@ def main():
             line["bvh_build"] = bvh_build_leg(rt, hs, cam, stats)
         except Exception as e:
             line["bvh_build"] = {"unavailable": repr(e)}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
