@@ -352,7 +352,7 @@ def main():
         except Exception as e:
             line["exact_mode_mrays_s"] = None
             line["exact_mode_error"] = repr(e)
-        if W * H * spp <= 2 * 3840 * 2160 * 64:   # the 8K / 1024-spp frame would take the reference kernel minutes
+        if W * H * spp <= 4 * 3840 * 2160 * 64:   # the 8K / 1024-spp frame would take the reference kernel minutes
             try:
                 line["reference_cuda"] = reference_cuda_leg(rt, scene, hs, cam, sp, pl, mt, tex, kms_max / args.steps)
             except Exception as e:

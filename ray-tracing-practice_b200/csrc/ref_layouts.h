@@ -1,5 +1,5 @@
 // ref_layouts.h -- byte images of the reference's host PODs as they cross the C-ABI (include/rt_b200.h).
-// Offsets measured against the compiled reference (oracle/_ref, ref_struct_sizes) in tests/test_layouts.py.
+// Offsets measured against the compiled reference (oracle/_ref, ref_struct_sizes) in tests/test_oracle_pins.py and tests/test_host.py (struct sizes and field offsets).
 #pragma once
 namespace rtb {
 struct SphereIn {  // SphereData, include/sphere.h:8-14 (32 B, align 16)

@@ -3,9 +3,10 @@
 // Stands where hit_scene -> hit_bvh -> {AABB::hit, hit_sphere, hit_plane} stand in the reference
 // (include/scene.h:23-35, include/bvh.h:19-65, include/aabb.h:42-65, include/sphere.h:24-53,
 // include/plane.h:57-96).  Differences by design:
-//   * nodes are 128-byte lines fetched as 8 x 128-bit loads (__ldg), the top levels from shared memory;
-//   * children are visited near-to-far (the reference's order is undefined) with a per-thread short
-//     stack in shared memory (spill to local memory only beyond kSmemStack entries);
+//   * nodes are 128-byte lines fetched as 7 x 128-bit loads through the L1 (__ldg); staging the top levels in shared memory
+//     is implemented (smem_top.cuh) and measured slower, so the production launch stages nothing;
+//   * children are visited near-to-far (the reference's order is undefined) with a per-thread stack of packed
+//     (entry distance, ref) pairs in LOCAL memory (L1-cached; a shared-memory front part is compiled out, RTB_SMEM_STACK = 0);
 //   * the slab test uses a per-ray reciprocal instead of 3 divides per node (include/aabb.h:44);
 //   * leaf tests only produce (t, primitive); normals / uv are derived once, after traversal;
 //   * acceptance follows the reference exactly: tmin <= t <= closest (Interval::contains, include/interval.h:16).
