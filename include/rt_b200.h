@@ -79,6 +79,11 @@ typedef struct rt_scene_stats {
     float input_upload_ms;      /* RT_BVH_GPU_LBVH: allocation + H2D of the caller's arrays (part of upload_ms) */
     int num_hoisted;            /* primitives kept out of the tree because they span most of the scene (the floor quad):
                                    tested once per ray before the traversal; at most 4 */
+    int grid_spheres;           /* spheres held by the uniform grid instead of the tree (0: no grid, the default).  With
+                                   RTB_GRID=1 in the environment the host builder puts a dense field of many similar small
+                                   spheres (>= 4096 and at least half of the scene's) into a grid; measured slower than the
+                                   tree on B200, kept as the measured alternative */
+    int grid_cells;             /* cells of that grid */
 } rt_scene_stats;
 
 /* Which builder replaces build_bvh (include/bvh_builder.h:99-120). */

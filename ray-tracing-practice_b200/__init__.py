@@ -68,7 +68,8 @@ class SceneStats(C.Structure):
     _fields_ = [("num_spheres", C.c_int), ("num_planes", C.c_int), ("num_materials", C.c_int), ("wide_nodes", C.c_int),
                 ("wide_depth", C.c_int), ("max_stack", C.c_int), ("leaves", C.c_int), ("sah_cost", C.c_float),
                 ("build_ms", C.c_float), ("upload_ms", C.c_float), ("device_bytes", C.c_ulonglong),
-                ("bvh_builder", C.c_int), ("input_upload_ms", C.c_float), ("num_hoisted", C.c_int)]
+                ("bvh_builder", C.c_int), ("input_upload_ms", C.c_float), ("num_hoisted", C.c_int),
+                ("grid_spheres", C.c_int), ("grid_cells", C.c_int)]
 
 
 class SceneOpts(C.Structure):

@@ -26,9 +26,6 @@
 #ifndef RTB_LOOP_SHAPE
 #define RTB_LOOP_SHAPE 4
 #endif
-#ifndef RTB_LEAF_K
-#define RTB_LEAF_K 12
-#endif
 #include "path.cuh"
 #include "smem_top.cuh"
 
@@ -36,7 +33,9 @@ namespace rtb {
 
 // TOP: the first sc.top_nodes wide nodes are read from shared memory (measured: no gain on B200 -- the L1 already holds
 // the top levels -- so the default launch uses TOP = false and saves the branch and two registers in the node loop)
-template <int MODE, bool X, bool COUNT, bool TOP>
+// GRID: the scene has a sphere grid (scene_pack.h): its own instantiation, so that scenes without one do not carry the
+// grid walk in their traversal loop (measured: compiled in but unused it cost the headline frame 15 %)
+template <int MODE, bool X, bool COUNT, bool TOP, bool GRID>
 __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(const __grid_constant__ DevScene sc,
                                                                                 const __grid_constant__ FrameParams fp) {
     extern __shared__ float4 smem4[];
@@ -184,6 +183,7 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
             if (start_ray) {
                 trav_reset(rt, 1e30f);  // Interval(0.001f, 1e30f), src/camera.cu:226
                 for (int k = 0; k < sc.num_hoisted; ++k) trav_leaf<X, COUNT>(sc, rt, wc, sc.hoisted[k]);
+                if (GRID) trav_grid_begin<X>(sc, rt);
             }
 #else
             if (start_ray) trav_begin<X, COUNT>(sc, rt, ps.o, ps.d, 0.001f, 1e30f, wc);  // Interval(0.001f, 1e30f), src/camera.cu:226
@@ -195,7 +195,8 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         // iteration, together with the lanes that were at wide nodes anyway.  Measured on B200: warp votes
         // that batch the leaf tests, lanes waiting for each other, and postponed leaves (below) all cost more than they save.
 #if RTB_LOOP_SHAPE == 1
-        while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {
+        while (ref_is_active(rt.ref)) {
+            if (GRID && ref_is_grid(rt.ref)) trav_grid_step<X, COUNT>(sc, rt, wc);
             if (ref_is_leaf(rt.ref)) trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
             if (ref_is_inner(rt.ref)) {
                 if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
@@ -206,37 +207,13 @@ __global__ void __launch_bounds__(kMegaThreads, kMegaBlocksPerSM) render_mega(co
         // shaded.  The unfinished lanes sit out the SHADE phase (predicated off) and resume here, next to the fresh rays of
         // the others -- the traversal runs with more lanes per instruction, the shading code runs more often.
         for (;;) {
-            const unsigned am = __ballot_sync(full, ref_is_leaf(rt.ref) || ref_is_inner(rt.ref));
+            const unsigned am = __ballot_sync(full, ref_is_active(rt.ref));
             if (am == 0u) break;
             if (__popc(am) < fp.trace_min && __any_sync(full, rt.ref == kRefDone)) break;
+            if (GRID && ref_is_grid(rt.ref)) trav_grid_step<X, COUNT>(sc, rt, wc);
             if (ref_is_leaf(rt.ref)) trav_leaf_pop<X, COUNT>(sc, rt, stk, wc);
             if (ref_is_inner(rt.ref)) {
                 if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
-            }
-        }
-#elif RTB_LOOP_SHAPE == 3
-        // speculative traversal: a lane that reaches a leaf postpones it (one slot) and goes on with its next node; the
-        // postponed leaves of the whole warp are tested together when a lane reaches its second leaf, when RTB_LEAF_K lanes
-        // hold one, or when no lane has a node left
-        {
-            int pend = 0;
-            for (;;) {
-                if (ref_is_inner(rt.ref)) {
-                    if (trav_inner<X, COUNT, TOP>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);
-                }
-                if (ref_is_leaf(rt.ref) && pend == 0) {
-                    pend = rt.ref;
-                    trav_pop(rt, stk);
-                }
-                const unsigned int ib = __ballot_sync(full, ref_is_inner(rt.ref)), mb = __ballot_sync(full, ref_is_leaf(rt.ref));
-                const unsigned int pb = __ballot_sync(full, pend != 0);
-                if (mb != 0u || ib == 0u || __popc(pb) >= RTB_LEAF_K) {
-                    if (pend != 0) {
-                        trav_leaf<X, COUNT>(sc, rt, wc, pend);
-                        pend = 0;
-                    }
-                }
-                if ((ib | mb) == 0u) break;
             }
         }
 #endif
@@ -257,17 +234,23 @@ size_t mega_smem_bytes(int top_nodes, int threads) {
     return (size_t)top_nodes * kTopStride * sizeof(float4) + (size_t)kSmemStack * threads * (sizeof(float) + sizeof(int));
 }
 
-template <int MODE, bool X, bool COUNT, bool TOP>
+template <int MODE, bool X, bool COUNT, bool TOP, bool GRID>
 static cudaError_t launch_mega_tt(const DevScene& sc, const FrameParams& fp, LaunchCfg cfg, cudaStream_t stream) {
     size_t smem = mega_smem_bytes(sc.top_nodes, cfg.threads);
-    cudaError_t e = cudaFuncSetAttribute(render_mega<MODE, X, COUNT, TOP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(render_mega<MODE, X, COUNT, TOP, GRID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    render_mega<MODE, X, COUNT, TOP><<<cfg.num_sms * cfg.blocks_per_sm, cfg.threads, smem, stream>>>(sc, fp);
+    render_mega<MODE, X, COUNT, TOP, GRID><<<cfg.num_sms * cfg.blocks_per_sm, cfg.threads, smem, stream>>>(sc, fp);
     return cudaGetLastError();
 }
 template <int MODE, bool X, bool COUNT>
 static cudaError_t launch_mega_t(const DevScene& sc, const FrameParams& fp, LaunchCfg cfg, cudaStream_t stream) {
-    return sc.top_nodes > 0 ? launch_mega_tt<MODE, X, COUNT, true>(sc, fp, cfg, stream) : launch_mega_tt<MODE, X, COUNT, false>(sc, fp, cfg, stream);
+    if (sc.grid_on) {  // nothing is staged in shared memory on this path
+        DevScene g = sc;
+        g.top_nodes = 0;
+        return launch_mega_tt<MODE, X, COUNT, false, true>(g, fp, cfg, stream);
+    }
+    return sc.top_nodes > 0 ? launch_mega_tt<MODE, X, COUNT, true, false>(sc, fp, cfg, stream)
+                            : launch_mega_tt<MODE, X, COUNT, false, false>(sc, fp, cfg, stream);
 }
 
 cudaError_t launch_render_mega(const DevScene& sc, const FrameParams& fp, int rng, int exact, int count, LaunchCfg cfg,
@@ -313,7 +296,8 @@ __global__ void __launch_bounds__(256, 2) trace_primary_kernel(const __grid_cons
             stk.tid = threadIdx.x; stk.nt = blockDim.x;
             RayTrav rt;
             trav_begin<false, false>(sc, rt, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), tmin, tmax, wc);
-            while (ref_is_leaf(rt.ref) || ref_is_inner(rt.ref)) {  // render_mega's TRACE loop (RTB_LOOP_SHAPE 1)
+            while (ref_is_active(rt.ref)) {  // render_mega's TRACE loop body
+                if (ref_is_grid(rt.ref)) trav_grid_step<false, false>(sc, rt, wc);
                 if (ref_is_leaf(rt.ref)) trav_leaf_pop<false, false>(sc, rt, stk, wc);
                 if (ref_is_inner(rt.ref)) {
                     if (trav_inner<false, false, true>(sc, s_top, stk, rt, wc)) trav_pop(rt, stk);

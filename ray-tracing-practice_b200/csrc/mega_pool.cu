@@ -230,6 +230,8 @@ __global__ void __launch_bounds__(kPoolThreads, kPoolBlocksPerSM) render_pool(co
             continue;  // refill before stepping
         }
         if (starve == full && ws.hit_cnt == 0 && ws.ready_cnt == 0) break;  // nothing parked, nothing ready, nobody tracing
+        // ---- GRID: one step of the sphere-grid walk (scenes with a grid, scene_pack.h)
+        if (ref_is_grid(rt.ref)) trav_grid_step<X, COUNT>(sc, rt, wc);
         // ---- LEAF: primitive tests, when enough lanes hold a leaf or no lane has an inner node to visit
         const unsigned lmask = __ballot_sync(full, ref_is_leaf(rt.ref));
         const unsigned imask = __ballot_sync(full, ref_is_inner(rt.ref));

@@ -128,7 +128,7 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         if ((rc = upload(&s->d_mats, tmp.mats.data(), tmp.mats.size() * sizeof(float), total))) return bail(rc);
     } else {
         // ---- wide BVH over conservative boxes + SoA primitive buffers in leaf order (host, scene_pack.cpp)
-        PackedScene pk = pack_scene(sp, S, pl, P, mt, M);
+        PackedScene pk = pack_scene(sp, S, pl, P, mt, M, -1);
         const WideBvh& bvh = pk.bvh;
         tree = {(int)bvh.nodes.size(), bvh.depth, bvh.max_stack, bvh.leaves, bvh.sah_cost, pk.build_ms};
         s->dev.num_hoisted = (int)bvh.hoisted_refs.size();
@@ -139,6 +139,21 @@ int rt_scene_create_ex(const void* spheres, int S, const void* planes, int P, co
         if ((rc = upload(&s->d_planes, pk.planes.data(), pk.planes.size() * sizeof(float), total))) return bail(rc);
         if ((rc = upload(&s->d_planes_fast, pk.planes_fast.data(), pk.planes_fast.size() * sizeof(float), total))) return bail(rc);
         if ((rc = upload(&s->d_mats, pk.mats.data(), pk.mats.size() * sizeof(float), total))) return bail(rc);
+        if (pk.grid.enabled) {
+            const GridAccel& g = pk.grid;
+            if ((rc = upload(&s->d_grid_cells, g.cells.data(), g.cells.size() * sizeof(unsigned int), total))) return bail(rc);
+            if ((rc = upload(&s->d_grid_refs, g.refs.data(), g.refs.size() * sizeof(int), total))) return bail(rc);
+            s->dev.grid_on = 1;
+            s->dev.grid_cells = (const uint2*)s->d_grid_cells;
+            s->dev.grid_refs = (const int*)s->d_grid_refs;
+            for (int a = 0; a < 3; ++a) {
+                s->dev.grid_lo[a] = g.lo[a]; s->dev.grid_hi[a] = g.hi[a]; s->dev.grid_cw[a] = g.cw[a];
+                s->dev.grid_icw[a] = 1.0f / g.cw[a]; s->dev.grid_n[a] = g.n[a];
+                s->dev.tree_lo[a] = g.tree_lo[a]; s->dev.tree_hi[a] = g.tree_hi[a];
+            }
+            s->stats.grid_spheres = (int)g.sphere_ids.size();
+            s->stats.grid_cells = g.n[0] * g.n[1] * g.n[2];
+        }
     }
     if (tree.max_stack > kSmemStack + kLocalStack) {
         fail(RT_ERR_UNSUPPORTED, "rt_scene_create: BVH needs a deeper traversal stack than the kernels provide");
@@ -242,7 +257,10 @@ int rt_scene_rebuild(rt_scene* s, const void* spheres, int S, const void* planes
         gpu_build_free(g);
         return fail(RT_ERR_UNSUPPORTED, "rt_scene_rebuild: BVH needs a deeper traversal stack than the kernels provide");
     }
-    void* old[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast};
+    void* old[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_grid_cells, s->d_grid_refs};
+    s->d_grid_cells = s->d_grid_refs = nullptr;  // the device builder puts everything in the tree
+    s->dev.grid_on = 0;
+    s->stats.grid_spheres = s->stats.grid_cells = 0;
     for (void* b : old)
         if (b) cudaFree(b);
     s->d_nodes = g.d_nodes;
@@ -280,7 +298,7 @@ void rt_scene_destroy(rt_scene* s) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     if (s->tex_obj) cudaDestroyTextureObject(s->tex_obj);
     if (s->tex_array) cudaFreeArray(s->tex_array);
-    void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_mats, s->d_tex, s->d_fb, s->d_u8,
+    void* bufs[] = {s->d_nodes, s->d_spheres, s->d_sphere_meta, s->d_planes, s->d_planes_fast, s->d_mats, s->d_tex, s->d_fb, s->d_u8, s->d_grid_cells, s->d_grid_refs,
                     s->d_tile_counter, s->d_counters, s->d_trace, s->wf.buf, s->d_acc, s->d_packed};
     for (void* b : bufs)
         if (b) cudaFree(b);

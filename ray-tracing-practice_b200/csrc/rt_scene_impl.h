@@ -68,6 +68,8 @@ struct rt_scene {
     void* d_planes_fast = nullptr;
     void* d_mats = nullptr;
     void* d_tex = nullptr;
+    void* d_grid_cells = nullptr;
+    void* d_grid_refs = nullptr;
     cudaArray_t tex_array = nullptr;
     cudaTextureObject_t tex_obj = 0;
     float* d_fb = nullptr;

@@ -32,6 +32,13 @@ struct DevScene {
     int top_nodes;                           // wide nodes [0, top_nodes) are staged in shared memory
     int num_hoisted;                         // primitives kept out of the tree (wide_bvh.h): tested once per ray in trav_begin
     int hoisted[4];                          // their leaf references
+    // uniform grid over a dense field of small spheres (scene_pack.h GridAccel); grid_on = 0: everything is in the tree
+    int grid_on;
+    const uint2* __restrict__ grid_cells;    // (first ref, count) per cell, x fastest
+    const int* __restrict__ grid_refs;       // leaf references of the spheres overlapping a cell
+    float grid_lo[3], grid_hi[3], grid_cw[3], grid_icw[3];
+    int grid_n[3];
+    float tree_lo[3], tree_hi[3];            // bounds of what the tree holds: a ray that misses them skips the tree
 };
 
 #ifndef RTB_SMEM_STACK
@@ -237,8 +244,12 @@ __device__ __forceinline__ bool plane_fast_t(V3 o, V3 d, const float4* __restric
 constexpr int kRefDone = 0x7fffffff;
 constexpr int kRefNeed = 0x7ffffffe;
 constexpr int kRefIdle = 0x7ffffffd;
+constexpr int kRefGrid = 0x7ffffffc;   // the ray is walking the sphere grid (trav_grid_step); the tree comes after it
 __device__ __forceinline__ bool ref_is_leaf(int r) { return r < 0; }
-__device__ __forceinline__ bool ref_is_inner(int r) { return (unsigned int)r < (unsigned int)kRefIdle; }
+__device__ __forceinline__ bool ref_is_inner(int r) { return (unsigned int)r < (unsigned int)kRefGrid; }
+__device__ __forceinline__ bool ref_is_grid(int r) { return r == kRefGrid; }
+// the ray still has traversal steps to do
+__device__ __forceinline__ bool ref_is_active(int r) { return (unsigned int)r - (unsigned int)kRefIdle > 2u; }
 
 struct RayTrav {
     V3 o, d;
@@ -249,6 +260,7 @@ struct RayTrav {
     int ref, sp;
     int htype, hslot, horig;             // closest hit so far: -1 miss / 0 sphere / 1 plane, re-ordered slot, caller's index
     unsigned int best_key;
+    int gcell, gcur, gend;               // grid walk: packed cell (x | y << 10 | z << 20), next / end position in its ref list
 };
 
 // per-thread stack: kSmemStack entries in shared memory (strided by the block size), the rest in local memory as
@@ -315,6 +327,9 @@ __device__ __forceinline__ void trav_reset(RayTrav& r, float tmax) {
     r.hslot = -1;
     r.horig = -1;
     r.best_key = 0;
+    r.gcell = 0;
+    r.gcur = 0;
+    r.gend = 0;
 }
 
 template <bool X>
@@ -476,6 +491,102 @@ __device__ __forceinline__ void trav_leaf(const DevScene& sc, RayTrav& r, WorkCo
     trav_leaf<X, COUNT>(sc, r, wc, r.ref);
 }
 
+// ---- sphere grid ---------------------------------------------------------------------------------------------
+// A ray's walk through the grid is a function of its cell alone: the parameter at which it leaves cell c along axis a is
+// t_a(c) = (lo_a + (c_a + [d_a > 0]) cw_a) id_a - o_a id_a, recomputed from the integer cell at every step (two FFMA per
+// axis on constants and the per-ray reciprocals the tree walk keeps anyway) instead of accumulated -- so a walk that is
+// interrupted (render_mega's time-sliced TRACE) and resumed takes exactly the steps of an uninterrupted one, and the
+// state is three integers.  The walk ends behind the first cell boundary that lies beyond the closest hit so far, or
+// where it leaves the grid; then the tree (planes, outlying spheres) is entered if the ray reaches its bounds at all.
+
+// slab test of [tmin, closest] against a box; nx/ny/nz-style selection is done with min/max here (boxes are not in node layout)
+template <bool X>
+__device__ __forceinline__ bool ray_box(const RayTrav& r, float lx, float ly, float lz, float hx, float hy, float hz) {
+    const float x0 = fmaf(lx, r.idx, -r.oox), x1 = fmaf(hx, r.idx, -r.oox);
+    const float y0 = fmaf(ly, r.idy, -r.ooy), y1 = fmaf(hy, r.idy, -r.ooy);
+    const float z0 = fmaf(lz, r.idz, -r.ooz), z1 = fmaf(hz, r.idz, -r.ooz);
+    const float tnear = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
+    const float tfar = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), r.closest));
+    return tnear <= fmaf(tfar, 1.0000005f, r.eps);  // the exact-mode guard of trav_inner, for both policies: these tests are rare
+}
+
+// what follows the grid walk (or the hoisted tests, without a grid): the tree's root, or nothing
+template <bool X>
+__device__ __forceinline__ int trav_tree_entry(const DevScene& sc, const RayTrav& r) {
+    if (!sc.grid_on) return 0;
+    return ray_box<X>(r, sc.tree_lo[0], sc.tree_lo[1], sc.tree_lo[2], sc.tree_hi[0], sc.tree_hi[1], sc.tree_hi[2]) ? 0 : kRefDone;
+}
+
+// enters the grid at the first cell the ray's [tmin, closest] interval reaches, or goes on to the tree
+template <bool X>
+__device__ __forceinline__ void trav_grid_begin(const DevScene& sc, RayTrav& r) {
+    const float x0 = fmaf(sc.grid_lo[0], r.idx, -r.oox), x1 = fmaf(sc.grid_hi[0], r.idx, -r.oox);
+    const float y0 = fmaf(sc.grid_lo[1], r.idy, -r.ooy), y1 = fmaf(sc.grid_hi[1], r.idy, -r.ooy);
+    const float z0 = fmaf(sc.grid_lo[2], r.idz, -r.ooz), z1 = fmaf(sc.grid_hi[2], r.idz, -r.ooz);
+    const float t0 = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), r.tmin));
+    const float t1 = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), r.closest));
+    if (!(t0 <= fmaf(t1, 1.0000005f, r.eps))) {
+        r.ref = trav_tree_entry<X>(sc, r);
+        return;
+    }
+    // entry cell: the cell of o + t0 d, clamped (a point on a face of the grid belongs to the cell inside)
+    const float px = fmaf(t0, r.d.x, r.o.x), py = fmaf(t0, r.d.y, r.o.y), pz = fmaf(t0, r.d.z, r.o.z);
+    int cx = (int)floorf((px - sc.grid_lo[0]) * sc.grid_icw[0]);
+    int cy = (int)floorf((py - sc.grid_lo[1]) * sc.grid_icw[1]);
+    int cz = (int)floorf((pz - sc.grid_lo[2]) * sc.grid_icw[2]);
+    cx = cx < 0 ? 0 : (cx >= sc.grid_n[0] ? sc.grid_n[0] - 1 : cx);
+    cy = cy < 0 ? 0 : (cy >= sc.grid_n[1] ? sc.grid_n[1] - 1 : cy);
+    cz = cz < 0 ? 0 : (cz >= sc.grid_n[2] ? sc.grid_n[2] - 1 : cz);
+    r.gcell = cx | (cy << 10) | (cz << 20);
+    r.gcur = 0;
+    r.gend = -1;  // "list of this cell not fetched yet"
+    r.ref = kRefGrid;
+}
+
+// one step of the walk: (move to the next cell and fetch its list)? then (one sphere of the list)?
+template <bool X, bool COUNT>
+__device__ __forceinline__ void trav_grid_step(const DevScene& sc, RayTrav& r, WorkCount& wc) {
+    if (r.gcur >= r.gend) {
+        int cx = r.gcell & 1023, cy = (r.gcell >> 10) & 1023, cz = r.gcell >> 20;
+        if (r.gend >= 0) {
+            // leave the cell through the nearest of its three far faces
+            const float ex = fmaf((float)(cx + (__float_as_int(r.idx) < 0 ? 0 : 1)), sc.grid_cw[0], sc.grid_lo[0]);
+            const float ey = fmaf((float)(cy + (__float_as_int(r.idy) < 0 ? 0 : 1)), sc.grid_cw[1], sc.grid_lo[1]);
+            const float ez = fmaf((float)(cz + (__float_as_int(r.idz) < 0 ? 0 : 1)), sc.grid_cw[2], sc.grid_lo[2]);
+            const float tx = fmaf(ex, r.idx, -r.oox), ty = fmaf(ey, r.idy, -r.ooy), tz = fmaf(ez, r.idz, -r.ooz);
+            const float tn = fminf(tx, fminf(ty, tz));
+            // a hit inside the cells walked so far ends the walk.  The guard keeps a hit that lies ON the face (within the
+            // rounding of tn) from ending it one cell early: a sphere overlapping the next cell could be nearer by less than that
+            bool out = r.closest < tn - fmaf(fabsf(tn), 4e-7f, r.eps);
+            if (!out) {
+                if (tx <= ty && tx <= tz) { cx += __float_as_int(r.idx) < 0 ? -1 : 1; out = (unsigned int)cx >= (unsigned int)sc.grid_n[0]; }
+                else if (ty <= tz) { cy += __float_as_int(r.idy) < 0 ? -1 : 1; out = (unsigned int)cy >= (unsigned int)sc.grid_n[1]; }
+                else { cz += __float_as_int(r.idz) < 0 ? -1 : 1; out = (unsigned int)cz >= (unsigned int)sc.grid_n[2]; }
+            }
+            if (out) {
+                r.ref = trav_tree_entry<X>(sc, r);
+                return;
+            }
+            r.gcell = cx | (cy << 10) | (cz << 20);
+        }
+        if (COUNT) wc.nodes++;  // a cell counts as a node visit
+        const uint2 h = __ldg(sc.grid_cells + ((size_t)cz * sc.grid_n[1] + cy) * sc.grid_n[0] + cx);
+        r.gcur = (int)h.x;
+        r.gend = (int)(h.x + h.y);
+    }
+    if (r.gcur < r.gend) {
+        const int ref = __ldg(sc.grid_refs + r.gcur);
+        ++r.gcur;
+        // the sphere's padded box first (make_prim_boxes' padding): what a tree would have culled is culled here too, so the
+        // fp32 discriminant's phantom hits OUTSIDE the box -- which the reference's own tree never reaches -- stay unreported
+        const float4 s = __ldg(sc.spheres + (ref & 0x0fffffff));
+        const float ar = fabsf(s.w);
+        const float m = fmaxf(fabsf(s.x), fmaxf(fabsf(s.y), fabsf(s.z)));
+        const float R = ar + fmaf(1e-3f, ar, 1e-6f * (m + ar));
+        if (ray_box<X>(r, s.x - R, s.y - R, s.z - R, s.x + R, s.y + R, s.z + R)) trav_leaf<X, COUNT>(sc, r, wc, ref);
+    }
+}
+
 // Start of a segment: per-ray constants, then the hoisted primitives (the few that span most of the scene, kept out of the
 // tree by the builder).  Callers reach this point with the warp converged (the SHADE phase of the megakernel), so the floor
 // quad -- which most rays hit -- is tested at full lane occupancy instead of as a 2-lanes-active leaf step, and `closest`
@@ -485,6 +596,7 @@ template <bool X, bool COUNT>
 __device__ __forceinline__ void trav_begin(const DevScene& sc, RayTrav& r, V3 o, V3 d, float tmin, float tmax, WorkCount& wc) {
     trav_init<X>(r, o, d, tmin, tmax);
     for (int k = 0; k < sc.num_hoisted; ++k) trav_leaf<X, COUNT>(sc, r, wc, sc.hoisted[k]);
+    if (sc.grid_on) trav_grid_begin<X>(sc, r);
 }
 
 // leaf step followed by the pop, with the top stack entry requested BEFORE the primitive test so that the two loads
@@ -525,6 +637,10 @@ __device__ __forceinline__ void trace_closest(const DevScene& sc, const float4* 
     RayTrav r;
     trav_begin<X, COUNT>(sc, r, o, d, tmin, tmax, wc);
     while (r.ref != kRefDone) {
+        if (ref_is_grid(r.ref)) {
+            trav_grid_step<X, COUNT>(sc, r, wc);
+            continue;
+        }
         bool pop = true;
         if (ref_is_leaf(r.ref)) trav_leaf<X, COUNT>(sc, r, wc);
         else pop = trav_inner<X, COUNT>(sc, s_top, stk, r, wc);

@@ -205,8 +205,20 @@ int emu_lbvh_check(const void* sp, int S, const void* pl, int P, int* out4) {
 int emu_scene_create2(const void* sp, int S, const void* pl, int P, const void* mt, int M, const float* tex, int tw, int th,
                       int tex_mat, int builder, void** out) {
     EmuScene* s = new EmuScene();
-    s->pk = pack_scene((const SphereIn*)sp, S, (const PlaneIn*)pl, P, (const MatIn*)mt, M);
+    // builder 0: host SAH tree; 1: the device builder's steps on the host; 2: host SAH tree + the sphere grid where it applies
+    s->pk = pack_scene((const SphereIn*)sp, S, (const PlaneIn*)pl, P, (const MatIn*)mt, M, builder == 2 ? 1 : 0);
     if (builder == 1) lbvh_build_host((const SphereIn*)sp, S, (const PlaneIn*)pl, P, s->pk);
+    if (s->pk.grid.enabled) {
+        const GridAccel& g = s->pk.grid;
+        s->dev.grid_on = 1;
+        s->dev.grid_cells = (const uint2*)g.cells.data();
+        s->dev.grid_refs = g.refs.data();
+        for (int a = 0; a < 3; ++a) {
+            s->dev.grid_lo[a] = g.lo[a]; s->dev.grid_hi[a] = g.hi[a]; s->dev.grid_cw[a] = g.cw[a];
+            s->dev.grid_icw[a] = 1.0f / g.cw[a]; s->dev.grid_n[a] = g.n[a];
+            s->dev.tree_lo[a] = g.tree_lo[a]; s->dev.tree_hi[a] = g.tree_hi[a];
+        }
+    }
     s->dev.nodes = (const float4*)s->pk.bvh.nodes.data();
     s->dev.spheres = (const float4*)s->pk.spheres.data();
     s->dev.sphere_meta = (const int2*)s->pk.sphere_meta.data();

@@ -231,3 +231,42 @@ def test_fast_plane_record_agrees_with_the_reference_arithmetic(emul, EmuSceneCl
     assert np.max(np.abs(t2[same] - t[same]) / t[same]) < 1e-4
     for k in range(3):
         assert (pl["type"][ix2[ty2 == 1]] == k).sum() > 50
+
+
+def test_sphere_grid_walk_finds_the_tree_walks_hits(emul, EmuSceneCls, orc, rt):
+    """the uniform grid over a dense sphere field (scene_pack.h GridAccel, traverse.cuh trav_grid_step; host run of the
+    device code): camera rays AND rays that start on surfaces inside the field -- the ones the grid is for -- get the ids
+    and t bits of the all-in-the-tree scene in exact mode, the oracle's exhaustive scan agrees on a sample, and the
+    production arithmetic differs from exact mode on at most 1e-5 of the rays"""
+    hs = rt.synthetic_scene(6000, W=320, H=180, seed=99)
+    sp, pl, mt, _ = hs.arrays()
+    tree = EmuSceneCls(emul, sp, pl, mt)
+    grid = EmuSceneCls(emul, sp, pl, mt, builder=2)
+    rays = rt.pixel_center_rays(hs.camera(0))
+    ty, ix, t = tree.trace(rays, exact=1)
+    hit = ty >= 0
+    assert hit.mean() > 0.3
+    # secondary rays: from the primary hit points, seeded directions over the whole sphere (half of them leave the field
+    # upwards, the others run along it or into the floor)
+    rng = np.random.default_rng(4)
+    p = rays[hit, :3] + t[hit, None] * rays[hit, 3:]
+    d = rng.normal(size=p.shape).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    sec = np.concatenate([p, d], axis=1).astype(np.float32)
+    for rr in (rays, sec):
+        a = tree.trace(rr, exact=1)
+        b = grid.trace(rr, exact=1)
+        assert (a[0] == b[0]).all() and (a[1] == b[1]).all() and (bits(a[2]) == bits(b[2])).all()
+        f = grid.trace(rr, exact=0)
+        assert ((f[0] != b[0]) | (f[1] != b[1])).mean() <= 1e-5
+        same = (f[0] == b[0]) & (f[1] == b[1]) & (b[0] >= 0)
+        # 1e-5 relative (north_star) on camera rays; a bounce ray's hit a few 1e-3 away is the difference of two numbers of
+        # size |oc|, so the bound is relative to the scene's unit there
+        assert np.max(np.abs(f[2][same] - b[2][same]) / np.maximum(b[2][same], 1.0 if rr is sec else 0.0)) <= 1e-5
+    sel = np.arange(0, len(sec), 37)
+    oy, oi, orec = orc.scene(sp, pl, mt).trace(sec[sel], 0)
+    by, bi, bt = grid.trace(sec[sel], exact=1)
+    mism = (by != oy) | (bi != oi)
+    assert mism.mean() <= 2e-3   # the scan's phantom grazing hits outside the boxes (test_gpu_gates_r02.py)
+    ok = ~mism & (oy >= 0)
+    assert (bits(bt[ok]) == bits(orec[ok, 0])).all()

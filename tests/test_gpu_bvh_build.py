@@ -192,3 +192,33 @@ def test_scene_rebuild_swaps_geometry_in_place(rt, orc):
     ty2, ix2, _ = sc.trace_primary(rays)  # a refused rebuild leaves the scene as it was
     assert (ty2 == ty).all() and (ix2 == ix).all()
     sc.close()
+
+
+def test_sphere_grid_scene_matches_the_tree_scene(rt, monkeypatch):
+    """RTB_GRID=1 (opt-in, measured slower: DESIGN.md 4.2): the dense sphere field goes into a uniform grid walked by
+    trav_grid_step, the rest stays in a small tree.  The closest hit does not depend on the structure: exact-mode ids and t
+    bits equal the all-in-the-tree scene's on every pixel-centre ray, the reference-stream frame is byte-identical, and the
+    production arithmetic differs on at most 1e-5 of the rays."""
+    hs = rt.synthetic_scene(10000, W=480, H=270, sqrt_spp=2, depth=8, seed=1234)
+    sp, pl, mt, _ = hs.arrays()
+    cam = hs.camera(0)
+    tree = rt.Scene(sp, pl, mt)
+    monkeypatch.setenv("RTB_GRID", "1")
+    grid = rt.Scene(sp, pl, mt)
+    monkeypatch.delenv("RTB_GRID")
+    st = grid.stats()
+    assert tree.stats()["grid_spheres"] == 0 and st["grid_spheres"] >= 9000 and st["grid_cells"] > 1000
+    assert st["wide_nodes"] < tree.stats()["wide_nodes"] // 10
+    rays = rt.pixel_center_rays(cam)
+    a, b = tree.trace_primary(rays), grid.trace_primary(rays)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all() and (bits(a[2]) == bits(b[2])).all()
+    f = grid.trace_primary(rays, exact=False)
+    assert ((f[0] != b[0]) | (f[1] != b[1])).mean() <= 1e-5
+    fa, ia = tree.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    fb, ib = grid.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    assert ia["segments"] == ib["segments"] and fa.tobytes() == fb.tobytes()
+    pa, _ = tree.render(cam, seed=5)
+    pb, _ = grid.render(cam, seed=5)
+    assert (bits(pa) == bits(pb)).all(-1).mean() >= 0.999
+    tree.close()
+    grid.close()
