@@ -161,7 +161,10 @@ def test_kernel_variants_agree(rt, test_scene):
 # ------------------------------------------------------------------ production stream (Philox): statistical gate 3
 def test_philox_converged_image_within_tolerance(rt, orc):
     """converged image vs the reference estimator (oracle, reference stream): per-channel MAE / PSNR on the mean image.
-    Tolerance (stated with the measurement): MAE <= 3 sigma of the two images' Monte-Carlo noise."""
+    Tolerance (stated with the measurement): per-channel MAE <= 1.5 x the MAE between two independently seeded GPU
+    renders (the Monte-Carlo noise floor) + 1e-4, image mean within 2 %, PSNR >= 45 dB (measured 50.5), and a signed-bias test:
+    |mean(GPU - oracle)| <= 4 sigma / sqrt(N) with sigma from the two GPU renders.  The stricter gates against the reference's
+    own CUDA render, per first-hit material class, are in test_gpu_gates_r02.py."""
     hs = rt.synthetic_scene(2000, W=160, H=90, sqrt_spp=24, depth=12, seed=77)
     sp, pl, mt, _ = hs.arrays()
     cam = hs.camera(0)
@@ -178,6 +181,14 @@ def test_philox_converged_image_within_tolerance(rt, orc):
     print("per-channel MAE vs oracle", mae, "noise floor", noise, "PSNR %.1f dB" % psnr)
     assert (mae <= 1.5 * noise + 1e-4).all()
     assert abs(ma.mean() - mo.mean()) <= 0.02 * mo.mean()
+    assert psnr >= 45.0
+    # signed bias over the whole image.  The oracle image carries its own noise (one render on the reference stream), so the
+    # per-pixel sigma of the difference is that of two independent renders: estimated from ma - mb
+    diff = (ma - mo).mean(-1)
+    sigma = (ma - mb).mean(-1).std()
+    z = diff.mean() / (sigma / np.sqrt(diff.size))
+    print("signed bias: mean diff %+.3e, z = %+.2f" % (diff.mean(), z))
+    assert abs(z) <= 4.0
     assert abs(ia["segments"] - so) <= 0.01 * so
     again, _ = sc.render(cam, seed=11)
     assert again.tobytes() == fa.tobytes()              # deterministic
@@ -296,3 +307,23 @@ def test_render_u8_is_render_plus_reference_output_stage(rt, test_scene):
     ref, _ = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
     u8, _ = sc.render_u8(cam, 2, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
     assert u8.tobytes() == rt.tonemap_host(g["fb_sum"], 2).tobytes() or (u8 != rt.tonemap_host(g["fb_sum"], 2)).mean() < 1e-3
+
+
+def test_time_sliced_trace_does_not_change_the_frame(rt, monkeypatch):
+    """render_mega's TRACE phase is time-sliced (a lane may be interrupted mid-traversal and resumed after the others were
+    shaded; FrameParams::trace_min, tuning knob RTB_TRACE_MIN): the schedule must not change a single byte -- production
+    stream (sample chunks, fixed-point accumulators) and reference stream (whole pixels, exact math) alike"""
+    hs = rt.synthetic_scene(3000, W=256, H=144, sqrt_spp=6, depth=12, seed=21)
+    sp, pl, mt, _ = hs.arrays()
+    cam = hs.camera(0)
+    sc = rt.Scene(sp, pl, mt)
+    want_p, ip = sc.render(cam, seed=9)
+    want_r, ir = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+    for k in ("1", "3", "16", "31", "32"):
+        monkeypatch.setenv("RTB_TRACE_MIN", k)
+        got_p, jp = sc.render(cam, seed=9)
+        got_r, jr = sc.render(cam, rng=rt.RNG_REFERENCE, exact=True, tex_mode=rt.TEX_CPU)
+        assert got_p.tobytes() == want_p.tobytes() and jp["segments"] == ip["segments"], k
+        assert got_r.tobytes() == want_r.tobytes() and jr["segments"] == ir["segments"], k
+    monkeypatch.delenv("RTB_TRACE_MIN")
+    sc.close()
