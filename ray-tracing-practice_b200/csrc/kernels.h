@@ -90,7 +90,7 @@ constexpr int kBlocksPerTile = kTile * kTile / kBlockPixels;
 constexpr int kMegaThreads = RTB_MEGA_THREADS;      // CTA size of render_mega
 constexpr int kMegaBlocksPerSM = RTB_MEGA_BLOCKS;   // resident CTAs per SM it is compiled (register-capped) for
 constexpr int kPoolThreads = 256, kPoolBlocksPerSM = 3;  // render_pool / wavefront kernels: the geometry they were measured with
-constexpr int kTraceMinDefault = 6;                 // time-sliced TRACE: see FrameParams::trace_min
+constexpr int kTraceMinDefault = 6, kTraceMinSmallTree = 10;  // time-sliced TRACE: see FrameParams::trace_min
 constexpr int kLeafMinDefault = 12;
 
 // persistent megakernel.  rng: 0 Philox / 1 reference stream; exact: 0/1; count: 0/1

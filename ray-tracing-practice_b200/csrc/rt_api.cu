@@ -431,7 +431,9 @@ int launch_frame(rt_scene* s, const void* cam76, const rt_render_opts* opts_in, 
     fp.park_min = 32;
     if (const char* e = getenv("RTB_REFILL_MIN")) fp.refill_min = atoi(e);
     if (const char* e = getenv("RTB_PARK_MIN")) fp.park_min = atoi(e);
-    fp.trace_min = kTraceMinDefault;
+    // small trees (the reference's shipped scene: 86 nodes, 3.6 visits per ray) finish a traversal in a few steps, so a TRACE
+    // phase is worth ending earlier: measured 255.9 ms at 10 vs 260.7 at 6 on the shipped scene, 179.0 vs 174.9 on the headline
+    fp.trace_min = s->dev.num_nodes < 1024 ? kTraceMinSmallTree : kTraceMinDefault;
     if (const char* e = getenv("RTB_TRACE_MIN")) fp.trace_min = atoi(e);
     fp.regroup = 0;
     if (const char* e = getenv("RTB_POOL_REGROUP")) fp.regroup = atoi(e) ? 1 : 0;
