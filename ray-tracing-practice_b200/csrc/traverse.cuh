@@ -195,14 +195,25 @@ __device__ __forceinline__ bool plane_t(V3 o, V3 d, const float4* __restrict__ p
 // two evaluations of alpha / beta (they agree to a few 1e-6) could fall on different sides.  Everywhere else the decision is
 // the reference's, and t differs from the reference's by fp32 rounding (~3e-7 relative: no cancellation in t's operands).
 constexpr float kEdgeEps = 1e-4f, kTieEps = 1e-6f;
+#ifndef RTB_NOINLINE_FALLBACK
+#define RTB_NOINLINE_FALLBACK 0
+#endif
+// the reference-order test as the fast test's fallback: rare (hits within kEdgeEps of an outline, near-parallel rays), and
+// inlined it is ~90 instructions at each of plane_fast_t's two exits times every place a leaf is tested
+#if RTB_NOINLINE_FALLBACK && defined(__CUDA_ARCH__)
+__device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+bool plane_fallback_t(V3 o, V3 d, const float4* __restrict__ p, float tmin, float tmax, float& t_out) {
+    float al, be;
+    return plane_t<false>(o, d, p, tmin, tmax, t_out, al, be);
+}
 __device__ __forceinline__ bool plane_fast_t(V3 o, V3 d, const float4* __restrict__ q, const float4* __restrict__ p, float tmin,
                                              float tmax, float& t_out) {
     const float4 nD = __ldg(q);
     const float denom = fmaf(nD.z, d.z, fmaf(nD.y, d.y, nD.x * d.x));
-    if (fabsf(denom) < 2e-8f) {  // (almost) parallel: the reference's own |denom| < 1e-8 rule decides
-        float al, be;
-        return plane_t<false>(o, d, p, tmin, tmax, t_out, al, be);
-    }
+    if (fabsf(denom) < 2e-8f) return plane_fallback_t(o, d, p, tmin, tmax, t_out);  // (almost) parallel: the reference's own |denom| < 1e-8 rule decides
     const float num = nD.w - fmaf(nD.z, o.z, fmaf(nD.y, o.y, nD.x * o.x));
     const float t = __fdividef(num, denom);
     // the same margin on t's interval: a hit within 1e-6 (relative) of tmin or of the closest hit so far is the reference's call
@@ -228,8 +239,7 @@ __device__ __forceinline__ bool plane_fast_t(V3 o, V3 d, const float4* __restric
         return true;
     }
     if (m < -kEdgeEps) return false;
-    float al, be;
-    return plane_t<false>(o, d, p, tmin, tmax, t_out, al, be);
+    return plane_fallback_t(o, d, p, tmin, tmax, t_out);
 }
 
 // ---- traversal ----------------------------------------------------------------------------------------------
